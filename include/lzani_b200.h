@@ -1,0 +1,139 @@
+/*
+ * lzani_b200.h -- C ABI of the B200-native LZ-ANI pair-comparison hot path.
+ *
+ * This is the drop-in boundary for the ONE path this repository accelerates: what
+ * CLZMatcher::do_matching (reference src/lz_matcher.cpp:172-277) does with its private
+ * CParser objects (reference src/parser.h:243-253):
+ *
+ *     CParser parser(params);                       -> lzani_create()
+ *     parser.prepare_reference(seq_view(ref), ..)   \
+ *     parser.prepare_data(seq_view(qry), ..)         |  lzani_set_sequences() once, then
+ *     parser.parse()                                 |-> lzani_run() / lzani_run_rows()
+ *     results_t r = parser.calc_stats()             /     (batch form: one call, all pairs)
+ *     vector<region_t> v = parser.get_parsing()     -> lzani_regions()   (--out-alignment only)
+ *
+ * Plain pointers and sizes only; no C++/torch types.  All work is done by hand-written
+ * sm_100a CUDA kernels; there is NO CPU fallback: every entry point fails with
+ * LZANI_ERR_CUDA when no usable device is present.
+ *
+ * Ids are indices into the array handed to lzani_set_sequences() (the reference uses the
+ * post-reorder reservoir index, lz_matcher.cpp:78-85).  "reference r / query q" follow the
+ * reference's direction convention: out[(r,q)] is the parse of q against the
+ * index of r.
+ */
+#ifndef LZANI_B200_H
+#define LZANI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LZANI_ABI_VERSION 1
+
+/* The eight parse parameters (reference src/params.h:38-45, defaults 11 7 40 40 35 15 7 3). */
+typedef struct lzani_params_t {
+    int32_t mal; /* min_anchor_len     --mal */
+    int32_t msl; /* min_seed_len       --msl */
+    int32_t mrd; /* max_dist_in_ref    --mrd */
+    int32_t mqd; /* max_dist_in_query  --mqd */
+    int32_t reg; /* min_region_len     --reg */
+    int32_t aw;  /* approx_window      --aw  */
+    int32_t am;  /* approx_mismatches  --am  */
+    int32_t ar;  /* approx_run_len     --ar  */
+} lzani_params_t;
+
+/* == results_t (reference src/defs.h:48-65): nt_match, nt_mismatch, num_alns. */
+typedef struct lzani_result_t {
+    int32_t sym_in_matches;
+    int32_t sym_in_literals;
+    int32_t no_components;
+} lzani_result_t;
+
+/* == region_t (reference src/defs.h:67-153), as returned by CParser::get_parsing(). */
+typedef struct lzani_region_t {
+    int32_t ref_start, ref_end;
+    int32_t seq_start, seq_end;
+    int32_t num_matches, num_mismatches;
+} lzani_region_t;
+
+/* Device timings of the last lzani_run*() call (CUDA events on the library's stream). */
+typedef struct lzani_timing_t {
+    double h2d_ms;      /* pair list (+ sequences if not yet resident) host->device */
+    double pack_ms;     /* K1: base-6 triples -> bit-plane records               */
+    double index_ms;    /* K2: anchor presence bitmap + anchor table build        */
+    double parse_ms;    /* K3: warp-per-pair parse                                */
+    double d2h_ms;      /* results device->host                                   */
+    double total_ms;    /* first event to last event                              */
+    uint64_t n_pairs;   /* ordered pairs processed                                */
+    uint64_t q_bases;   /* sum of query lengths over those pairs                  */
+    uint64_t r_bases;   /* sum over indexed references of Dr = 2*Lr + 3*mrd       */
+    uint64_t h2d_bytes; /* bytes copied host->device inside the call              */
+    uint64_t d2h_bytes; /* bytes copied device->host inside the call              */
+    uint32_t launches;  /* kernels launched inside the call                       */
+    uint32_t n_batches; /* reference batches the index memory budget forced       */
+} lzani_timing_t;
+
+enum {
+    LZANI_OK = 0,
+    LZANI_ERR_ARG = 1,    /* bad argument / unsupported parameter combination */
+    LZANI_ERR_CUDA = 2,   /* CUDA runtime error or no device                  */
+    LZANI_ERR_STATE = 3,  /* call order (e.g. run before set_sequences)       */
+    LZANI_ERR_NOMEM = 4   /* host or device allocation failed                 */
+};
+
+typedef struct lzani_ctx lzani_ctx;
+
+/* Replaces `CParser parser(params)` (parser.h:237-241).  device_ids/n_devices: the CUDA
+ * device this context drives (n_devices must be 1: one context -- and one process -- per
+ * GPU; device_ids==NULL means the current device).  Returns LZANI_OK or an error code; on
+ * error *ctx is still a valid object holding the message when allocation was possible. */
+int lzani_create(lzani_ctx** ctx, const lzani_params_t* params, const int* device_ids, int n_devices);
+
+/* Replaces the seq_view hand-off of prepare_reference/prepare_data (parser.cpp:16-50).
+ * data[i] = sequence i in the reservoir's default `three_in_byte` packing
+ * (seq_reservoir.cpp:39-57: byte = 36a+6b+c, symbols 0..3 = ACGT, 4/5 = N, last partial
+ * byte high-aligned), len[i] = number of bases.  The bytes are copied; the caller may free
+ * them after the call returns.  May be called again to replace the set. */
+int lzani_set_sequences(lzani_ctx* ctx, uint32_t n, const uint8_t* const* data, const uint32_t* len);
+
+/* Replaces the whole worker loop of do_matching (lz_matcher.cpp:192-269).
+ * CSR pair list: for reference r in [0, n_refs) the queries are
+ * q_ids[row_off[r] .. row_off[r+1]); n_refs must equal the number of sequences.
+ * q_ids == NULL means all2all: every q != r in increasing q (row_off ignored, may be NULL).
+ * out[k] receives the result of the k-th (r, q) in CSR order.  Blocking. */
+int lzani_run(lzani_ctx* ctx, uint32_t n_refs, const uint64_t* row_off, const uint32_t* q_ids,
+              lzani_result_t* out);
+
+/* Same, for a subset of reference rows (the multi-GPU shard of one rank):
+ * row j is reference ref_ids[j]; q_ids==NULL again means every q != ref_ids[j]. */
+int lzani_run_rows(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
+                   const uint32_t* q_ids, lzani_result_t* out);
+
+/* Device-resident variant used to time the kernels alone: runs the same rows `repeat`
+ * times back to back without copying results to the host; the last pass's results are
+ * left on the device and copied to `out` only if out != NULL. */
+int lzani_run_rows_resident(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids,
+                            const uint64_t* row_off, const uint32_t* q_ids, int repeat,
+                            lzani_result_t* out);
+
+/* Replaces parser.get_parsing() (parser.h:250-253, parser.cpp:786-837) for ONE ordered
+ * pair: writes up to `cap` regions (sorted as the reference sorts them) and stores the
+ * full count in *n_regions. */
+int lzani_regions(lzani_ctx* ctx, uint32_t ref_id, uint32_t q_id, lzani_region_t* out, uint32_t cap,
+                  uint32_t* n_regions);
+
+int lzani_get_timing(const lzani_ctx* ctx, lzani_timing_t* t);
+
+/* Bytes of device memory the index batches may use (default: 60% of free memory). */
+int lzani_set_index_budget(lzani_ctx* ctx, uint64_t bytes);
+
+const char* lzani_last_error(const lzani_ctx* ctx);
+void lzani_destroy(lzani_ctx* ctx);
+int lzani_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LZANI_B200_H */
