@@ -10,7 +10,8 @@
  *     parser.prepare_data(seq_view(qry), ..)         |  lzani_set_sequences() once, then
  *     parser.parse()                                 |-> lzani_run() / lzani_run_rows()
  *     results_t r = parser.calc_stats()             /     (batch form: one call, all pairs)
- *     vector<region_t> v = parser.get_parsing()     -> lzani_regions()   (--out-alignment only)
+ *     vector<region_t> v = parser.get_parsing()     -> not yet covered (--out-alignment only;
+ *                                                       SURVEY 8f-2, a "next" row)
  *
  * Plain pointers and sizes only; no C++/torch types.  All work is done by hand-written
  * sm_100a CUDA kernels; there is NO CPU fallback: every entry point fails with
@@ -117,12 +118,6 @@ int lzani_run_rows(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids, con
 int lzani_run_rows_resident(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids,
                             const uint64_t* row_off, const uint32_t* q_ids, int repeat,
                             lzani_result_t* out);
-
-/* Replaces parser.get_parsing() (parser.h:250-253, parser.cpp:786-837) for ONE ordered
- * pair: writes up to `cap` regions (sorted as the reference sorts them) and stores the
- * full count in *n_regions. */
-int lzani_regions(lzani_ctx* ctx, uint32_t ref_id, uint32_t q_id, lzani_region_t* out, uint32_t cap,
-                  uint32_t* n_regions);
 
 int lzani_get_timing(const lzani_ctx* ctx, lzani_timing_t* t);
 

@@ -1,0 +1,183 @@
+"""lz-ani_b200 -- B200-native LZ-ANI pair-comparison hot path (host-side Python binding).
+
+The product is `liblzani_b200.so` (hand-written sm_100a CUDA behind the C ABI of
+include/lzani_b200.h).  This module is the thin ctypes mirror of that ABI plus the small
+host helpers tests and bench.py need (hostio: three_in_byte packing, FASTA, reorder; synth:
+seeded synthetic genome sets).  There is no CPU fallback: if the shared library is missing
+or no CUDA device is present, constructing `Matcher` raises.
+
+Import with importlib because of the hyphen in the directory name:
+
+    lz = importlib.import_module("lz-ani_b200")
+    m = lz.Matcher(params=None, device=0)
+    m.set_sequences(seqset)              # hostio.SeqSet
+    res = m.all2all()                    # (n*(n-1), 3) int32: nt_match, nt_mismatch, num_alns
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from . import hostio, synth  # noqa: F401
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "liblzani_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "capi.cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "simt.h")] + [
+        os.path.join(ROOT, "include", "lzani_b200.h")]
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + srcs + ["-o", LIB_PATH]
+    subprocess.run(cmd, check=True)
+    return LIB_PATH
+
+
+class TimingStruct(C.Structure):
+    _fields_ = [("h2d_ms", C.c_double), ("pack_ms", C.c_double), ("index_ms", C.c_double), ("parse_ms", C.c_double),
+                ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("n_pairs", C.c_uint64), ("q_bases", C.c_uint64),
+                ("r_bases", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("launches", C.c_uint32), ("n_batches", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class LzaniError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen the in-tree CUDA library; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise LzaniError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                         "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    lib.lzani_abi_version.restype = C.c_int
+    lib.lzani_create.argtypes = [C.POINTER(vp), vp, vp, C.c_int]
+    lib.lzani_set_sequences.argtypes = [vp, u32, vp, vp]
+    lib.lzani_run.argtypes = [vp, u32, vp, vp, vp]
+    lib.lzani_run_rows.argtypes = [vp, u32, vp, vp, vp, vp]
+    lib.lzani_run_rows_resident.argtypes = [vp, u32, vp, vp, vp, C.c_int, vp]
+    lib.lzani_get_timing.argtypes = [vp, C.POINTER(TimingStruct)]
+    lib.lzani_set_index_budget.argtypes = [vp, u64]
+    lib.lzani_last_error.argtypes = [vp]
+    lib.lzani_last_error.restype = C.c_char_p
+    lib.lzani_destroy.argtypes = [vp]
+    lib.lzani_destroy.restype = None
+    _lib = lib
+    return lib
+
+
+class Matcher:
+    """Mirror of what CLZMatcher::do_matching does with its CParser objects
+    (reference src/lz_matcher.cpp:172-277), batch form."""
+
+    def __init__(self, params: dict | None = None, device: int | None = None):
+        self.lib = load_library()
+        self.params = hostio.params_array(params)
+        self.h = C.c_void_p()
+        dev = None
+        if device is not None:
+            dev = (C.c_int * 1)(int(device))
+        rc = self.lib.lzani_create(C.byref(self.h), self.params.ctypes.data, dev, 1 if device is not None else 0)
+        if rc != 0:
+            msg = self.lib.lzani_last_error(self.h).decode() if self.h else "allocation failed"
+            if self.h:
+                self.lib.lzani_destroy(self.h)
+                self.h = None
+            raise LzaniError(f"lzani_create failed ({rc}): {msg}")
+        self.n = 0
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            raise LzaniError(f"{what} failed ({rc}): {self.lib.lzani_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lzani_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_index_budget(self, nbytes: int):
+        self._check(self.lib.lzani_set_index_budget(self.h, int(nbytes)), "lzani_set_index_budget")
+
+    def set_sequences(self, ss: "hostio.SeqSet"):
+        n = len(ss)
+        ptrs = (C.c_void_p * max(n, 1))()
+        for i, p in enumerate(ss.packed):
+            ptrs[i] = p.ctypes.data
+        lens = np.ascontiguousarray(ss.lens, dtype=np.uint32)
+        self._check(self.lib.lzani_set_sequences(self.h, n, ptrs, lens.ctypes.data), "lzani_set_sequences")
+        self.n = n
+
+    def timing(self) -> dict:
+        t = TimingStruct()
+        self._check(self.lib.lzani_get_timing(self.h, C.byref(t)), "lzani_get_timing")
+        return t.as_dict()
+
+    def all2all(self) -> np.ndarray:
+        out = np.zeros((self.n * max(self.n - 1, 0), 3), dtype=np.int32)
+        self._check(self.lib.lzani_run(self.h, self.n, None, None, out.ctypes.data), "lzani_run")
+        return out
+
+    def run(self, row_off, q_ids) -> np.ndarray:
+        row_off = np.ascontiguousarray(row_off, dtype=np.uint64)
+        q_ids = np.ascontiguousarray(q_ids, dtype=np.uint32)
+        out = np.zeros((int(row_off[-1] - row_off[0]), 3), dtype=np.int32)
+        self._check(self.lib.lzani_run(self.h, self.n, row_off.ctypes.data, q_ids.ctypes.data, out.ctypes.data), "lzani_run")
+        return out
+
+    def run_rows(self, rows, row_off=None, q_ids=None, out: np.ndarray | None = None, resident_repeat: int = 0):
+        """rows: reference ids; (row_off, q_ids) CSR over those rows or None for every q != r.
+        resident_repeat > 0 -> lzani_run_rows_resident (kernels only, `repeat` passes)."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        if q_ids is None:
+            n_pairs = rows.size * max(self.n - 1, 0)
+            off_p = q_p = None
+        else:
+            row_off = np.ascontiguousarray(row_off, dtype=np.uint64)
+            q_ids = np.ascontiguousarray(q_ids, dtype=np.uint32)
+            n_pairs = int(row_off[-1] - row_off[0])
+            off_p, q_p = row_off.ctypes.data, q_ids.ctypes.data
+        if out is None:
+            out = np.zeros((n_pairs, 3), dtype=np.int32)
+        assert out.shape == (n_pairs, 3) and out.dtype == np.int32 and out.flags.c_contiguous
+        if resident_repeat > 0:
+            self._check(self.lib.lzani_run_rows_resident(self.h, rows.size, rows.ctypes.data, off_p, q_p,
+                                                         int(resident_repeat), out.ctypes.data), "lzani_run_rows_resident")
+        else:
+            self._check(self.lib.lzani_run_rows(self.h, rows.size, rows.ctypes.data, off_p, q_p, out.ctypes.data),
+                        "lzani_run_rows")
+        return out
+
+
+def shard_rows(n_refs: int, rank: int, world: int) -> np.ndarray:
+    """Reference rows of one rank: r mod world == rank over the length-descending ids, so every
+    rank gets the same length mix (the reference's task unit is one reference row,
+    lz_matcher.cpp:200-209)."""
+    return np.arange(rank, n_refs, world, dtype=np.uint32)

@@ -1,0 +1,441 @@
+// capi.cu -- the C ABI of include/lzani_b200.h: context, HBM residency of the sequence set,
+// reference-row batching under the index memory budget, launches, timing.
+//
+// There is no CPU fallback here: without a CUDA device every entry point returns
+// LZANI_ERR_CUDA with a message.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/lzani_b200.h"
+#include "kernels.h"
+
+using namespace lzani;
+
+struct lzani_ctx {
+    Prm P{};
+    int device = -1;
+    int n_sm = 0;
+    int blocks_per_sm = 1;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // sequence set (resident)
+    uint32_t n_seqs = 0;
+    std::vector<SeqMeta> meta;
+    uint64_t n_recs = 0;
+    uint8_t* d_src = nullptr;
+    SeqMeta* d_meta = nullptr;
+    uint64_t* d_rec_base = nullptr;
+    Rec* d_recs = nullptr;
+    double pack_ms = 0;          // of the last set_sequences
+    uint64_t seq_h2d_bytes = 0;
+
+    // index pools for the current batch
+    uint64_t budget = 0;
+    uint32_t* d_bitmap = nullptr; uint64_t bitmap_words_cap = 0;
+    uint64_t* d_table = nullptr;  uint64_t table_slots_cap = 0;
+
+    // pair list + results
+    uint32_t* d_row_ref = nullptr; RefIndex* d_row_idx = nullptr; uint64_t* d_row_off = nullptr;
+    uint32_t* d_blk_base = nullptr; uint64_t rows_cap = 0;
+    uint32_t* d_q_ids = nullptr; uint64_t q_cap = 0;
+    void* d_out = nullptr; uint64_t out_cap = 0;
+    unsigned long long* d_counter = nullptr;
+
+    cudaEvent_t ev[8]{};
+    lzani_timing_t timing{};
+};
+
+namespace {
+
+int fail(lzani_ctx* c, int code, const std::string& msg)
+{
+    if (c) c->err = msg;
+    return code;
+}
+#define LZ_CUDA(c, call)                                                                         \
+    do {                                                                                         \
+        cudaError_t e_ = (call);                                                                 \
+        if (e_ != cudaSuccess)                                                                   \
+            return fail((c), e_ == cudaErrorMemoryAllocation ? LZANI_ERR_NOMEM : LZANI_ERR_CUDA, \
+                        std::string(#call) + ": " + cudaGetErrorString(e_));                     \
+    } while (0)
+
+template <class T>
+int ensure(lzani_ctx* c, T*& p, uint64_t& cap, uint64_t need)
+{
+    if (need <= cap && p) return LZANI_OK;
+    if (p) { cudaFree(p); p = nullptr; cap = 0; }
+    if (!need) need = 1;
+    LZ_CUDA(c, cudaMalloc((void**)&p, need * sizeof(T)));
+    cap = need;
+    return LZANI_OK;
+}
+
+void free_sequences(lzani_ctx* c)
+{
+    cudaFree(c->d_src); c->d_src = nullptr;
+    cudaFree(c->d_meta); c->d_meta = nullptr;
+    cudaFree(c->d_rec_base); c->d_rec_base = nullptr;
+    cudaFree(c->d_recs); c->d_recs = nullptr;
+    c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
+}
+
+float ms_between(cudaEvent_t a, cudaEvent_t b)
+{
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+}  // namespace
+
+extern "C" int lzani_abi_version(void) { return LZANI_ABI_VERSION; }
+
+extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int* device_ids, int n_devices)
+{
+    if (!out) return LZANI_ERR_ARG;
+    *out = nullptr;
+    lzani_ctx* c = new (std::nothrow) lzani_ctx();
+    if (!c) return LZANI_ERR_NOMEM;
+    *out = c;
+    if (!p) return fail(c, LZANI_ERR_ARG, "params == NULL");
+    if (n_devices > 1) return fail(c, LZANI_ERR_ARG, "one context drives one GPU: n_devices must be 1 (use one process per GPU)");
+    c->P = Prm{p->mal, p->msl, p->mrd, p->mqd, p->reg, p->aw, p->am, p->ar};
+    const Prm& P = c->P;
+    // what the kernels support (the reference has no explicit limits except mal <= 32, parser.cpp:59)
+    if (P.mal < 1 || P.mal > 32) return fail(c, LZANI_ERR_ARG, "mal must be in [1,32]");
+    if (P.msl < 1 || P.msl > 32) return fail(c, LZANI_ERR_ARG, "msl must be in [1,32]");
+    if (P.mrd < 1 || P.mrd > 100000) return fail(c, LZANI_ERR_ARG, "mrd must be in [1,100000]");
+    if (P.mqd < 0 || P.mqd > 1000) return fail(c, LZANI_ERR_ARG, "mqd must be in [0,1000]");
+    if (P.aw < 1 || P.aw > 32) return fail(c, LZANI_ERR_ARG, "aw must be in [1,32]");
+    if (P.ar < 1 || P.ar > 32) return fail(c, LZANI_ERR_ARG, "ar must be in [1,32]");
+    if (P.am < 0) return fail(c, LZANI_ERR_ARG, "am must be >= 0");
+
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(c, LZANI_ERR_CUDA, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                                           " (this library has no CPU fallback)");
+    int dev = 0;
+    if (device_ids && n_devices == 1) dev = device_ids[0];
+    else LZ_CUDA(c, cudaGetDevice(&dev));
+    if (dev < 0 || dev >= n_dev) return fail(c, LZANI_ERR_ARG, "device id out of range");
+    LZ_CUDA(c, cudaSetDevice(dev));
+    c->device = dev;
+    cudaDeviceProp prop;
+    LZ_CUDA(c, cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) return fail(c, LZANI_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; the kernels are built for sm_100a only");
+    c->n_sm = prop.multiProcessorCount;
+    LZ_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (auto& ev : c->ev) LZ_CUDA(c, cudaEventCreate(&ev));
+    LZ_CUDA(c, cudaMalloc((void**)&c->d_counter, sizeof(unsigned long long)));
+    c->blocks_per_sm = parse_blocks_per_sm();
+    return LZANI_OK;
+}
+
+extern "C" void lzani_destroy(lzani_ctx* c)
+{
+    if (!c) return;
+    if (c->device >= 0) {
+        cudaSetDevice(c->device);
+        free_sequences(c);
+        cudaFree(c->d_bitmap); cudaFree(c->d_table);
+        cudaFree(c->d_row_ref); cudaFree(c->d_row_idx); cudaFree(c->d_row_off); cudaFree(c->d_blk_base);
+        cudaFree(c->d_q_ids); cudaFree(c->d_out); cudaFree(c->d_counter);
+        for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+        if (c->stream) cudaStreamDestroy(c->stream);
+    }
+    delete c;
+}
+
+extern "C" const char* lzani_last_error(const lzani_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+extern "C" int lzani_set_index_budget(lzani_ctx* c, uint64_t bytes)
+{
+    if (!c) return LZANI_ERR_ARG;
+    c->budget = bytes;
+    return LZANI_OK;
+}
+
+extern "C" int lzani_get_timing(const lzani_ctx* c, lzani_timing_t* t)
+{
+    if (!c || !t) return LZANI_ERR_ARG;
+    *t = c->timing;
+    return LZANI_OK;
+}
+
+extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len)
+{
+    if (!c) return LZANI_ERR_ARG;
+    if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
+    if (n && (!data || !len)) return fail(c, LZANI_ERR_ARG, "data/len == NULL");
+    LZ_CUDA(c, cudaSetDevice(c->device));
+    free_sequences(c);
+    const Prm& P = c->P;
+    std::vector<SeqMeta> meta(n);
+    std::vector<uint64_t> rec_base((size_t)n + 1, 0);
+    uint64_t src_bytes = 0, recs = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        // positions are 32-bit ints in the reference (combined reference 2L+3mrd < 2^31)
+        if ((uint64_t)len[i] * 2 + 3ull * (uint64_t)P.mrd >= 0x7FFFFF00ull)
+            return fail(c, LZANI_ERR_ARG, "sequence too long for 32-bit positions");
+        if (len[i] && !data[i]) return fail(c, LZANI_ERR_ARG, "data[i] == NULL");
+        meta[i].src_off = src_bytes;
+        meta[i].len = len[i];
+        meta[i].pad_ = 0;
+        meta[i].q_rec = recs;
+        meta[i].r_rec = recs + (uint64_t)q_form_recs((int)len[i], P.mrd);
+        rec_base[i] = recs;
+        recs = meta[i].r_rec + (uint64_t)r_form_recs((int)len[i], P.mrd);
+        src_bytes += ((uint64_t)len[i] + 2) / 3;
+    }
+    rec_base[n] = recs;
+
+    // stage the reservoir bytes contiguously in pinned memory, one H2D copy
+    uint8_t* h_src = nullptr;
+    LZ_CUDA(c, cudaMallocHost((void**)&h_src, src_bytes ? src_bytes : 1));
+    for (uint32_t i = 0; i < n; ++i)
+        if (len[i]) memcpy(h_src + meta[i].src_off, data[i], ((size_t)len[i] + 2) / 3);
+
+    int rc = LZANI_OK;
+    do {
+        cudaError_t e;
+#define LZ_TRY(call) if ((e = (call)) != cudaSuccess) { rc = fail(c, e == cudaErrorMemoryAllocation ? LZANI_ERR_NOMEM : LZANI_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e)); break; }
+        LZ_TRY(cudaMalloc((void**)&c->d_src, src_bytes ? src_bytes : 1));
+        LZ_TRY(cudaMalloc((void**)&c->d_meta, sizeof(SeqMeta) * (n ? n : 1)));
+        LZ_TRY(cudaMalloc((void**)&c->d_rec_base, sizeof(uint64_t) * ((size_t)n + 1)));
+        LZ_TRY(cudaMalloc((void**)&c->d_recs, sizeof(Rec) * (recs ? recs : 1)));
+        LZ_TRY(cudaEventRecord(c->ev[0], c->stream));
+        LZ_TRY(cudaMemcpyAsync(c->d_src, h_src, src_bytes, cudaMemcpyHostToDevice, c->stream));
+        LZ_TRY(cudaMemcpyAsync(c->d_meta, meta.data(), sizeof(SeqMeta) * n, cudaMemcpyHostToDevice, c->stream));
+        LZ_TRY(cudaMemcpyAsync(c->d_rec_base, rec_base.data(), sizeof(uint64_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, c->stream));
+        LZ_TRY(cudaEventRecord(c->ev[1], c->stream));
+        LZ_TRY(launch_pack(c->stream, c->d_src, c->d_meta, c->d_rec_base, n, recs, P.mrd, c->d_recs));
+        LZ_TRY(cudaEventRecord(c->ev[2], c->stream));
+        LZ_TRY(cudaStreamSynchronize(c->stream));
+#undef LZ_TRY
+    } while (0);
+    cudaFreeHost(h_src);
+    if (rc != LZANI_OK) { free_sequences(c); return rc; }
+    c->n_seqs = n;
+    c->n_recs = recs;
+    c->meta.swap(meta);
+    c->pack_ms = ms_between(c->ev[1], c->ev[2]);
+    c->seq_h2d_bytes = src_bytes + sizeof(SeqMeta) * n + sizeof(uint64_t) * ((size_t)n + 1);
+    c->timing = lzani_timing_t{};
+    c->timing.h2d_ms = ms_between(c->ev[0], c->ev[1]);
+    c->timing.pack_ms = c->pack_ms;
+    c->timing.h2d_bytes = c->seq_h2d_bytes;
+    c->timing.launches = recs ? 1 : 0;
+    return LZANI_OK;
+}
+
+namespace {
+
+struct RowPlan {
+    uint64_t bitmap_words, table_slots;   // 0 for rows without pairs
+    uint32_t bbits, tbits, blocks;
+};
+
+// The whole hot path for a set of reference rows.  `repeat` > 1 re-runs index build + parse
+// with everything resident (bench "value" leg).
+int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off_in,
+                  const uint32_t* q_ids, int repeat, lzani_result_t* out, bool copy_out)
+{
+    if (!c) return LZANI_ERR_ARG;
+    if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
+    if (!c->d_recs) return fail(c, LZANI_ERR_STATE, "lzani_set_sequences has not been called");
+    if (q_ids && !row_off_in) return fail(c, LZANI_ERR_ARG, "q_ids given without row_off");
+    if (copy_out && !out) return fail(c, LZANI_ERR_ARG, "out == NULL");
+    if (repeat < 1) repeat = 1;
+    LZ_CUDA(c, cudaSetDevice(c->device));
+    const Prm& P = c->P;
+    const uint32_t n = c->n_seqs;
+
+    // ---- row table on the host
+    std::vector<uint32_t> row_ref(n_rows);
+    std::vector<uint64_t> row_off((size_t)n_rows + 1, 0);
+    uint64_t q_bases = 0, r_bases = 0, total_len = 0;
+    for (uint32_t i = 0; i < n; ++i) total_len += c->meta[i].len;
+    for (uint32_t j = 0; j < n_rows; ++j) {
+        const uint32_t r = ref_ids ? ref_ids[j] : j;
+        if (r >= n) return fail(c, LZANI_ERR_ARG, "reference id out of range");
+        row_ref[j] = r;
+        if (q_ids) {
+            if (row_off_in[j + 1] < row_off_in[j]) return fail(c, LZANI_ERR_ARG, "row_off is not non-decreasing");
+            row_off[j + 1] = row_off_in[j + 1] - row_off_in[0];
+        } else {
+            row_off[j + 1] = row_off[j] + (n ? n - 1 : 0);
+            q_bases += total_len - c->meta[r].len;
+        }
+    }
+    const uint64_t n_pairs = row_off[n_rows];
+    const uint32_t* q_src = q_ids ? q_ids + row_off_in[0] : nullptr;
+    if (q_ids)
+        for (uint64_t k = 0; k < n_pairs; ++k) {
+            if (q_src[k] >= n) return fail(c, LZANI_ERR_ARG, "query id out of range");
+            q_bases += c->meta[q_src[k]].len;
+        }
+    std::vector<RowPlan> plan(n_rows);
+    for (uint32_t j = 0; j < n_rows; ++j) {
+        RowPlan& rp = plan[j];
+        rp = RowPlan{0, 0, 0, 0, 0};
+        if (row_off[j + 1] == row_off[j]) continue;
+        const int Dr = r_form_len((int)c->meta[row_ref[j]].len, P.mrd);
+        rp.bbits = index_bbits(Dr, P.mal);
+        rp.tbits = index_tbits(Dr);
+        rp.bitmap_words = std::max<uint64_t>(1, ((uint64_t)1 << rp.bbits) / 32);
+        rp.table_slots = (uint64_t)1 << rp.tbits;
+        rp.blocks = (uint32_t)((Dr + 255) / 256);
+        r_bases += (uint64_t)Dr;
+    }
+
+    // ---- device buffers for the pair list and the results
+    if (c->rows_cap < (uint64_t)n_rows + 1) {
+        cudaFree(c->d_row_ref); cudaFree(c->d_row_idx); cudaFree(c->d_row_off); cudaFree(c->d_blk_base);
+        c->d_row_ref = nullptr; c->d_row_idx = nullptr; c->d_row_off = nullptr; c->d_blk_base = nullptr;
+        c->rows_cap = 0;
+        const uint64_t need = (uint64_t)n_rows + 1;
+        LZ_CUDA(c, cudaMalloc((void**)&c->d_row_ref, need * sizeof(uint32_t)));
+        LZ_CUDA(c, cudaMalloc((void**)&c->d_row_idx, need * sizeof(RefIndex)));
+        LZ_CUDA(c, cudaMalloc((void**)&c->d_row_off, need * sizeof(uint64_t)));
+        LZ_CUDA(c, cudaMalloc((void**)&c->d_blk_base, need * sizeof(uint32_t)));
+        c->rows_cap = need;
+    }
+    if (q_ids) if (int rc = ensure(c, c->d_q_ids, c->q_cap, n_pairs)) return rc;
+    {
+        uint64_t cap_bytes = c->out_cap;
+        uint8_t* p = (uint8_t*)c->d_out;
+        if (int rc = ensure(c, p, cap_bytes, n_pairs * sizeof(lzani_result_t))) return rc;
+        c->d_out = p; c->out_cap = cap_bytes;
+    }
+
+    // ---- batches of consecutive rows under the index budget
+    uint64_t budget = c->budget;
+    if (!budget) {
+        size_t fr = 0, tot = 0;
+        LZ_CUDA(c, cudaMemGetInfo(&fr, &tot));
+        fr += c->bitmap_words_cap * 4 + c->table_slots_cap * 8;   // pools we may re-use
+        budget = (uint64_t)(0.6 * (double)fr);
+    }
+    struct Batch { uint32_t a, b; uint64_t words, slots; };
+    std::vector<Batch> batches;
+    {
+        Batch cur{0, 0, 0, 0};
+        for (uint32_t j = 0; j < n_rows; ++j) {
+            const uint64_t bytes = plan[j].bitmap_words * 4 + plan[j].table_slots * 8;
+            if (bytes > budget) return fail(c, LZANI_ERR_NOMEM, "the index of one reference exceeds the index budget");
+            if ((cur.words + plan[j].bitmap_words) * 4 + (cur.slots + plan[j].table_slots) * 8 > budget && cur.b > cur.a) {
+                batches.push_back(cur);
+                cur = Batch{j, j, 0, 0};
+            }
+            cur.b = j + 1;
+            cur.words += plan[j].bitmap_words;
+            cur.slots += plan[j].table_slots;
+        }
+        if (cur.b > cur.a) batches.push_back(cur);
+    }
+    uint64_t max_words = 1, max_slots = 1;
+    for (const Batch& b : batches) { max_words = std::max(max_words, b.words); max_slots = std::max(max_slots, b.slots); }
+    if (int rc = ensure(c, c->d_bitmap, c->bitmap_words_cap, max_words)) return rc;
+    if (int rc = ensure(c, c->d_table, c->table_slots_cap, max_slots)) return rc;
+
+    lzani_timing_t T{};
+    T.n_batches = (uint32_t)batches.size();
+    cudaStream_t st = c->stream;
+
+    // ---- H2D: the pair list
+    LZ_CUDA(c, cudaEventRecord(c->ev[0], st));
+    LZ_CUDA(c, cudaMemcpyAsync(c->d_row_ref, row_ref.data(), sizeof(uint32_t) * n_rows, cudaMemcpyHostToDevice, st));
+    LZ_CUDA(c, cudaMemcpyAsync(c->d_row_off, row_off.data(), sizeof(uint64_t) * ((size_t)n_rows + 1), cudaMemcpyHostToDevice, st));
+    T.h2d_bytes += sizeof(uint32_t) * n_rows + sizeof(uint64_t) * ((size_t)n_rows + 1);
+    if (q_ids && n_pairs) {
+        LZ_CUDA(c, cudaMemcpyAsync(c->d_q_ids, q_src, sizeof(uint32_t) * n_pairs, cudaMemcpyHostToDevice, st));
+        T.h2d_bytes += sizeof(uint32_t) * n_pairs;
+    }
+    LZ_CUDA(c, cudaEventRecord(c->ev[1], st));
+
+    const int grid = c->n_sm * c->blocks_per_sm;
+    std::vector<RefIndex> h_idx;
+    std::vector<uint32_t> h_blk;
+    for (int rep = 0; rep < repeat; ++rep) {
+        for (const Batch& b : batches) {
+            const uint32_t nb = b.b - b.a;
+            h_idx.assign(nb, RefIndex{0, 0, 0, 0});
+            h_blk.assign((size_t)nb + 1, 0);
+            uint64_t w = 0, s = 0;
+            for (uint32_t j = 0; j < nb; ++j) {
+                const RowPlan& rp = plan[b.a + j];
+                h_idx[j] = RefIndex{w, s, rp.bbits, rp.tbits};
+                w += rp.bitmap_words;
+                s += rp.table_slots;
+                h_blk[j + 1] = h_blk[j] + rp.blocks;
+            }
+            LZ_CUDA(c, cudaEventRecord(c->ev[2], st));
+            LZ_CUDA(c, cudaMemcpyAsync(c->d_row_idx + b.a, h_idx.data(), sizeof(RefIndex) * nb, cudaMemcpyHostToDevice, st));
+            LZ_CUDA(c, cudaMemcpyAsync(c->d_blk_base, h_blk.data(), sizeof(uint32_t) * ((size_t)nb + 1), cudaMemcpyHostToDevice, st));
+            T.h2d_bytes += sizeof(RefIndex) * nb + sizeof(uint32_t) * ((size_t)nb + 1);
+            LZ_CUDA(c, cudaEventRecord(c->ev[3], st));
+            if (b.words) LZ_CUDA(c, cudaMemsetAsync(c->d_bitmap, 0, b.words * 4, st));
+            if (b.slots) LZ_CUDA(c, cudaMemsetAsync(c->d_table, 0xFF, b.slots * 8, st));
+            LZ_CUDA(c, launch_build_index(st, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a, c->d_blk_base,
+                                          nb, h_blk[nb], P, c->d_bitmap, c->d_table));
+            LZ_CUDA(c, cudaEventRecord(c->ev[4], st));
+            LZ_CUDA(c, cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned long long), st));
+            LZ_CUDA(c, launch_parse(st, grid, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
+                                    c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a], row_off[b.b], P,
+                                    c->d_bitmap, c->d_table, c->d_counter, c->d_out));
+            LZ_CUDA(c, cudaEventRecord(c->ev[5], st));
+            LZ_CUDA(c, cudaStreamSynchronize(st));
+            T.h2d_ms += ms_between(c->ev[2], c->ev[3]);
+            T.index_ms += ms_between(c->ev[3], c->ev[4]);
+            T.parse_ms += ms_between(c->ev[4], c->ev[5]);
+            T.launches += (h_blk[nb] ? 1 : 0) + (row_off[b.b] > row_off[b.a] ? 1 : 0);
+        }
+    }
+    LZ_CUDA(c, cudaEventRecord(c->ev[6], st));
+    if (out && n_pairs) {
+        LZ_CUDA(c, cudaMemcpyAsync(out, c->d_out, n_pairs * sizeof(lzani_result_t), cudaMemcpyDeviceToHost, st));
+        T.d2h_bytes = n_pairs * sizeof(lzani_result_t);
+    }
+    LZ_CUDA(c, cudaEventRecord(c->ev[7], st));
+    LZ_CUDA(c, cudaStreamSynchronize(st));
+    T.h2d_ms += ms_between(c->ev[0], c->ev[1]);
+    T.d2h_ms = ms_between(c->ev[6], c->ev[7]);
+    T.total_ms = ms_between(c->ev[0], c->ev[7]);
+    T.n_pairs = n_pairs * (uint64_t)repeat;
+    T.q_bases = q_bases * (uint64_t)repeat;
+    T.r_bases = r_bases * (uint64_t)repeat;
+    c->timing = T;
+    return LZANI_OK;
+}
+
+}  // namespace
+
+extern "C" int lzani_run(lzani_ctx* c, uint32_t n_refs, const uint64_t* row_off, const uint32_t* q_ids,
+                         lzani_result_t* out)
+{
+    if (!c) return LZANI_ERR_ARG;
+    if (c->d_recs && n_refs != c->n_seqs) return fail(c, LZANI_ERR_ARG, "n_refs must equal the number of sequences");
+    return run_rows_impl(c, n_refs, nullptr, row_off, q_ids, 1, out, true);
+}
+
+extern "C" int lzani_run_rows(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
+                              const uint32_t* q_ids, lzani_result_t* out)
+{
+    return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, 1, out, true);
+}
+
+extern "C" int lzani_run_rows_resident(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids,
+                                       const uint64_t* row_off, const uint32_t* q_ids, int repeat,
+                                       lzani_result_t* out)
+{
+    return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, repeat, out, false);
+}

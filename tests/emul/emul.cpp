@@ -1,0 +1,114 @@
+// TEST ONLY.  Host emulation of the CUDA path's SOURCE: compiles lz-ani_b200/csrc/{layout.h,
+// parse_core.h} with the HostWarp policy of simt.h (32 lanes run as a loop) so that the kernel
+// logic can be checked against the oracle on a machine without a GPU (`pytest -m "not gpu"`).
+// This is not a CPU fallback: it is built only by tests/emul/Makefile into
+// tests/emul/liblzani_emul.so, is never linked into liblzani_b200.so and is ~100x slower than
+// the reference.  The library itself fails loudly without a CUDA device.
+#include <atomic>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../lz-ani_b200/csrc/parse_core.h"
+
+using namespace lzani;
+
+namespace {
+
+struct HostSeq {
+    std::vector<Rec> q, r;
+    int len = 0;
+};
+struct HostIndex {
+    std::vector<uint32_t> bitmap;
+    std::vector<uint64_t> table;
+    uint32_t bbits = 0, tbits = 0;
+};
+
+void build_seq(HostSeq& s, const uint8_t* src, uint32_t len, const Prm& P)
+{
+    s.len = (int)len;
+    int nq = q_form_recs((int)len, P.mrd), nr = r_form_recs((int)len, P.mrd);
+    s.q.resize(nq);
+    s.r.resize(nr);
+    for (int i = 0; i < nq; ++i) s.q[i] = pack_q_record(src, len, (uint32_t)i);
+    for (int i = 0; i < nr; ++i) s.r[i] = pack_r_record(src, len, (uint32_t)P.mrd, (uint32_t)i);
+}
+
+// same element logic as the K2 kernel (kernels.cu: k_build_index)
+void build_index(HostIndex& ix, const HostSeq& s, const Prm& P)
+{
+    const int Dr = r_form_len(s.len, P.mrd);
+    ix.bbits = index_bbits(Dr, P.mal);
+    ix.tbits = index_tbits(Dr);
+    ix.bitmap.assign(((size_t)1 << ix.bbits) / 32 ? ((size_t)1 << ix.bbits) / 32 : 1, 0u);
+    ix.table.assign((size_t)1 << ix.tbits, LZ_EMPTY);
+    const uint32_t tmask = (1u << ix.tbits) - 1u;
+    for (int pos = 0; pos < Dr; ++pos) {
+        uint64_t key;
+        if (!ref_kmer_at(s.r.data(), Dr, pos, P.mal, key)) continue;
+        const uint32_t b = bitmap_index(key, P.mal, ix.bbits);
+        ix.bitmap[b >> 5] |= 1u << (b & 31u);
+        uint32_t h = table_home(key, ix.tbits);
+        const uint64_t e = ((uint64_t)table_tag(key, P.mal) << 32) | (uint32_t)pos;
+        // insertion order is scrambled on purpose: the parse must not depend on chain order
+        while (ix.table[h] != LZ_EMPTY) h = (h + 1u) & tmask;
+        ix.table[h] = e;
+    }
+}
+
+}  // namespace
+
+extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const uint8_t* const* data,
+                                      const uint32_t* len, uint32_t n_rows, const uint32_t* ref_ids,
+                                      const uint64_t* row_off, const uint32_t* q_ids, int32_t* out3,
+                                      int n_threads)
+{
+    Prm P{p8[0], p8[1], p8[2], p8[3], p8[4], p8[5], p8[6], p8[7]};
+    if (n_threads <= 0) n_threads = 1;
+    std::vector<HostSeq> seqs(n_seqs);
+    for (uint32_t i = 0; i < n_seqs; ++i) build_seq(seqs[i], data[i], len[i], P);
+    std::vector<uint64_t> dense;
+    if (!q_ids) {
+        dense.assign((size_t)n_rows + 1, 0);
+        for (uint32_t j = 0; j < n_rows; ++j) dense[j + 1] = dense[j] + (n_seqs ? n_seqs - 1 : 0);
+        row_off = dense.data();
+    }
+    std::atomic<uint64_t> next{0};
+    auto worker = [&]() {
+        HostWarp w;
+        HostIndex ix;
+        for (;;) {
+            uint64_t j = next.fetch_add(1);
+            if (j >= n_rows) break;
+            uint32_t r = ref_ids ? ref_ids[j] : (uint32_t)j;
+            uint64_t k = row_off[j];
+            if (row_off[j + 1] == k) continue;
+            build_index(ix, seqs[r], P);
+            auto one = [&](uint32_t q) {
+                PairView pv;
+                pv.q = seqs[q].q.data(); pv.Dq = seqs[q].len + P.mrd;
+                pv.r = seqs[r].r.data(); pv.Dr = r_form_len(seqs[r].len, P.mrd);
+                pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
+                pv.table = ix.table.data(); pv.tbits = ix.tbits;
+                PairResult res = parse_pair(w, pv, P);
+                out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
+                ++k;
+            };
+            if (q_ids) for (uint64_t e = row_off[j]; e < row_off[j + 1]; ++e) one(q_ids[e]);
+            else for (uint32_t q = 0; q < n_seqs; ++q) if (q != r) one(q);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < n_threads; ++t) pool.emplace_back(worker);
+    worker();
+    for (auto& th : pool) th.join();
+    return 0.0;
+}
+
+extern "C" int lzani_emul_regions(const int32_t*, const uint8_t*, uint32_t, const uint8_t*, uint32_t, int32_t*,
+                                  uint32_t, int32_t*)
+{
+    return -1;   // regions are not emulated
+}

@@ -103,3 +103,14 @@ class RefShim(_Checker):
     @staticmethod
     def available() -> bool:
         return os.path.exists(REF_SO)
+
+
+EMUL_SO = os.path.join(ROOT, "tests", "emul", "liblzani_emul.so")
+
+
+class Emul(_Checker):
+    """Host emulation of the CUDA kernel SOURCE (tests/emul/emul.cpp) -- test only."""
+
+    def __init__(self):
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "tests", "emul")], check=True)
+        super().__init__(EMUL_SO, "lzani_emul")
