@@ -73,7 +73,7 @@ def test_sparse_csr_rows_and_batched_index_budget():
                 assert got[k].tolist() == dense[r * (n - 1) + (qq if qq < r else qq - 1)].tolist()
                 k += 1
         # a tiny index budget forces one reference per batch; results must not change
-        m.set_index_budget(3 << 20)
+        m.set_index_budget(12 << 20)
         got2 = m.all2all()
         assert m.timing()["n_batches"] > 1
         assert np.array_equal(got2, dense)
