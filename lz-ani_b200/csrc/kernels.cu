@@ -89,6 +89,8 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
               int3* __restrict__ out)
 {
     DevWarp w((int)(threadIdx.x & 31u));
+    __shared__ uint16_t hit_list[LZ_PARSE_THREADS / 32][32];
+    uint16_t* list = hit_list[threadIdx.x >> 5];
     for (;;) {
         unsigned long long k = 0;
         if (w.lane == 0) k = atomicAdd(counter, 1ull);
@@ -113,7 +115,7 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
         pv.bbits = ix.bbits;
         pv.table = table_pool + ix.table_slot;
         pv.tbits = ix.tbits;
-        const PairResult res = parse_pair(w, pv, P);
+        const PairResult res = parse_pair(w, pv, P, list);
         if (w.lane == 0) out[k] = make_int3(res.m, res.x, res.n);
     }
 }

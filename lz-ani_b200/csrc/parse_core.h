@@ -348,6 +348,151 @@ LZ_HD uint64_t run_starts(uint64_t E, int n)   // bit k set <=> bits k..k+n-1 of
     return t;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// 64 bases of the three planes starting at pos (three 128-bit loads)
+struct Planes64 { uint32_t lo0, lo1, hi0, hi1, nm0, nm1; };
+LZ_HD Planes64 ext64(const Rec* s, int pos)
+{
+    const int wd = pos >> 5, sh = pos & 31;
+    const Rec a = ld_rec(s + wd), b = ld_rec(s + wd + 1), c = ld_rec(s + wd + 2);
+    Planes64 o;
+    o.lo0 = funnel_r(a.x, b.x, sh); o.lo1 = funnel_r(b.x, c.x, sh);
+    o.hi0 = funnel_r(a.y, b.y, sh); o.hi1 = funnel_r(b.y, c.y, sh);
+    o.nm0 = funnel_r(a.z, b.z, sh); o.nm1 = funnel_r(b.z, c.z, sh);
+    return o;
+}
+// equality word of two 64-base windows (bit t = bases t equal, N never equal)
+LZ_HD uint64_t equal64(const Planes64& a, const Planes64& b)
+{
+    const uint32_t m0 = (a.lo0 ^ b.lo0) | (a.hi0 ^ b.hi0) | a.nm0 | b.nm0;
+    const uint32_t m1 = (a.lo1 ^ b.lo1) | (a.hi1 ^ b.hi1) | a.nm1 | b.nm1;
+    return ~(((uint64_t)m1 << 32) | m0);
+}
+
+// Equality word of one diagonal of a prediction-mode chunk: bit k <-> q[i0+k] == r[P0+d+k]
+// with Q = ext64(q, i0).  Bits k < -d (reference positions before P0) are 0.
+LZ_HD uint64_t diag_equal64(const PairView& pv, const Planes64& Q, int i0, int P0, int d)
+{
+    const int rp = P0 + d;
+    if (rp >= 0) {
+        if (rp >= pv.Dr) return 0;
+        uint64_t e = equal64(Q, ext64(pv.r, rp));
+        if (d < 0) e &= ~low_mask64(-d);
+        return e;
+    }
+    return diag_equal_bits(pv, i0, P0, d);    // the window starts before the reference does (rare)
+}
+
+// ------------------------------------------------------------------------------------------
+// Approximate extension inside ONE stream word, evaluated by a single lane (the speculative
+// per-hit path).  mw: bit j = mismatch at stream position j; nv <= 32 positions exist in this
+// word; `more`: the stream continues behind it.  Same rule as approx_extend() above
+// (try_extend_forward/backward, parser.cpp:377-441).  `examined` = positions the sequential
+// walk would have looked at; complete == false when the walk would run on into the next word.
+struct ExtWord { int len, matches, examined; bool complete; };
+LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const Prm& P)
+{
+    ExtWord o;
+    o.len = 0; o.matches = 0; o.examined = 0; o.complete = true;
+    if (nv <= 0) return o;
+    const uint32_t m = mw & low_mask32(nv);
+    int brk = -1;
+    {
+        // the window can only overflow at a mismatch, and not before the (am+1)-th one
+        uint32_t t = m;
+        for (int c = 0; c < P.am && t; ++c) t &= t - 1u;
+        const uint64_t x = (uint64_t)m << 32;          // positions before the stream: matches
+        const uint64_t wmask = low_mask64(P.aw);
+        while (t) {
+            const int j = ctz32(t);
+            if (popc64((x >> (33 + j - P.aw)) & wmask) > P.am) { brk = j; break; }
+            t &= t - 1u;
+        }
+    }
+    const int end = brk >= 0 ? brk + 1 : nv;
+    o.examined = end;
+    o.complete = brk >= 0 || !more;
+    const uint64_t y = ~((uint64_t)m << 32);
+    uint64_t t = y;
+    for (int s = 1; s < P.ar; ++s) t &= y << s;
+    const uint32_t ok = (uint32_t)(t >> 32) & low_mask32(end);
+    if (ok) {
+        o.len = 32 - clz32(ok);
+        o.matches = popc32(~m & low_mask32(o.len));
+    }
+    return o;
+}
+
+// ------------------------------------------------------------------------------------------
+// One anchor hit, evaluated by ONE lane ahead of the sequential walk.  The result depends only
+// on the query position p (not on the parse state): the longest reference occurrence of the
+// mal-mer at p (ties -> smallest position, parser.cpp:516-530), and -- should the walk take it
+// as a match -- the approximate extension behind it (parser.cpp:691-695) and in front of it
+// (:659-672, valid when the literal run before p is at least `examined` long).  Anything that
+// does not fit one 32-base word (long matches, long extensions, long probe chains) is left to
+// the warp-cooperative routines above by setting HIT_DEFER / clearing HIT_FWD / HIT_BWD.
+//
+//   w2: [0,6) anchor length  [6,12) fwd ext  [12,18) fwd matches  + flags
+//   w3: [0,6) bwd ext        [6,12) bwd matches  [12,18) bwd positions examined
+constexpr uint32_t HIT_LIVE = 1u << 18;    // there is (or may be) an anchor at this position
+constexpr uint32_t HIT_DEFER = 1u << 19;   // evaluate with anchor_lookup() when reached
+constexpr uint32_t HIT_FWD = 1u << 20;     // fwd fields valid
+constexpr uint32_t HIT_BWD = 1u << 21;     // bwd fields valid
+constexpr int HIT_MAX_CHAIN = 6;           // matching-tag slots one lane inspects before deferring
+
+LZ_HD void eval_hit(const PairView& pv, const Prm& P, int p, uint32_t& o_pos, uint32_t& o_w2, uint32_t& o_w3)
+{
+    o_pos = 0; o_w2 = 0; o_w3 = 0;
+    uint32_t lo, hi, nm;
+    ext3(pv.q, p, lo, hi, nm);
+    if (nm & low_mask32(P.mal)) return;
+    const uint64_t key = kmer_key(lo, hi, P.mal);
+    const uint32_t tmask = (1u << pv.tbits) - 1u;
+    const uint32_t tag = table_tag(key, P.mal);
+    uint32_t h = table_home(key, pv.tbits);
+    int best_len = 0, best_pos = 0, seen = 0;
+    bool defer = false;
+    for (;;) {
+        const uint64_t slot = ld_u64(pv.table + (h & tmask));
+        if (slot == LZ_EMPTY) break;
+        if ((uint32_t)(slot >> 32) == tag) {
+            if (++seen > HIT_MAX_CHAIN) { defer = true; break; }
+            const int rp = (int)(uint32_t)slot;
+            uint32_t rl, rh, rn;
+            ext3(pv.r, rp, rl, rh, rn);
+            const uint32_t m0 = (lo ^ rl) | (hi ^ rh) | nm | rn;
+            if (!m0) { defer = true; break; }            // >= 32 equal bases
+            const int len = ctz32(m0);
+            if (len >= P.mal && (len > best_len || (len == best_len && rp < best_pos))) { best_len = len; best_pos = rp; }
+        }
+        ++h;
+    }
+    if (defer) { o_w2 = HIT_LIVE | HIT_DEFER; return; }
+    if (!best_len) return;
+    o_pos = (uint32_t)best_pos;
+    uint32_t w2 = HIT_LIVE | (uint32_t)best_len, w3 = 0;
+    {   // forward
+        const int qn = p + best_len, pn = best_pos + best_len;
+        int lim = pv.Dq - qn;
+        if (pv.Dr - pn < lim) lim = pv.Dr - pn;
+        const uint32_t mw = lim > 0 ? mism32(pv.q, pv.Dq, qn, pv.r, pv.Dr, pn) : 0xFFFFFFFFu;
+        const ExtWord e = extend_in_word(mw, lim > 32 ? 32 : lim, lim > 32, P);
+        if (e.complete) w2 |= HIT_FWD | ((uint32_t)e.len << 6) | ((uint32_t)e.matches << 12);
+    }
+    {   // backward
+        const int lim = p < best_pos ? p : best_pos;
+        BwdStream bs{&pv, p, best_pos};
+        const uint32_t mw = lim > 0 ? bs.word(0) : 0xFFFFFFFFu;
+        const ExtWord e = extend_in_word(mw, lim > 32 ? 32 : lim, lim > 32, P);
+        if (e.complete) {
+            w2 |= HIT_BWD;
+            w3 = (uint32_t)e.len | ((uint32_t)e.matches << 6) | ((uint32_t)e.examined << 12);
+        }
+    }
+    o_w2 = w2; o_w3 = w3;
+}
+
 struct ParseState {
     int i, pred, lit;            // query position, ref_pred_pos (<0: none), cur_lit_run_len
     int rs, re, kept_end;        // prev_region_start / prev_region_end / end of last kept region
@@ -355,10 +500,11 @@ struct ParseState {
     int totM, totX, totN;        // kept regions so far
 };
 
-// One match found at query position qi (parser.cpp:626-698), counts only.
+// One match found at query position qi (parser.cpp:626-698), counts only.  (w2, w3) is the
+// speculative record of eval_hit() when the match IS that anchor, else w2 == 0.
 template <class W>
 LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int qi, int lit_k, int pred_k,
-                      int best_pos, int best_len)
+                      int best_pos, int best_len, uint32_t w2, uint32_t w3)
 {
     int dist = best_pos - pred_k;
     if (dist < 0) dist = -dist;
@@ -383,17 +529,25 @@ LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int
             int lim = run;
             if (qi < lim) lim = qi;
             if (best_pos < lim) lim = best_pos;
-            BwdStream bs{&pv, qi, best_pos};
-            approx_extend(w, bs, lim, P, back, bm);
+            if ((w2 & HIT_BWD) && lim >= (int)((w3 >> 12) & 63u)) {
+                back = (int)(w3 & 63u);
+                bm = (int)((w3 >> 6) & 63u);
+            } else {
+                BwdStream bs{&pv, qi, best_pos};
+                approx_extend(w, bs, lim, P, back, bm);
+            }
         }
         s.curM = bm + best_len;
         s.curX = back - bm;
         s.rs = qi - back;
     }
-    int qn = qi + best_len;
-    int pn = best_pos + best_len;
+    const int qn = qi + best_len;
+    const int pn = best_pos + best_len;
     int fwd = 0, fm = 0;
-    {
+    if (w2 & HIT_FWD) {
+        fwd = (int)((w2 >> 6) & 63u);
+        fm = (int)((w2 >> 12) & 63u);
+    } else {
         int lim = pv.Dq - qn;
         if (pv.Dr - pn < lim) lim = pv.Dr - pn;
         FwdStream fs{&pv, qn, pn};
@@ -407,9 +561,76 @@ LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int
     s.re = s.i;
 }
 
-// ---- the whole pair.
+// best seed at chunk position k (parser.cpp:548-580): longest; ties -> closest to the
+// prediction, then smallest position.  Lanes own diagonals.
 template <class W>
-LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P)
+LZ_HD void best_seed(W& w, const PairView& pv, const Prm& P, const Planes64& Q, int i0, int P0, int lit0, int k,
+                     int d_lo, int d_hi, int& best_pos, int& best_len)
+{
+    int sl = 0;
+    uint32_t skey = 0xFFFFFFFFu;
+    const int qi = i0 + k;
+    for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
+        typename W::template Lanes<int> len, more;
+        typename W::template Lanes<uint32_t> dk;
+        LZ_EACH(w, ln)
+        {
+            const int d = dbase + ln;
+            len[ln] = 0;
+            more[ln] = 0;
+            dk[ln] = 0xFFFFFFFFu;
+            if (d < d_hi && d >= -k) {
+                const uint64_t E = diag_equal64(pv, Q, i0, P0, d);
+                if ((run_starts(E, P.msl) >> k) & 1ull) {
+                    const uint64_t z = ~(E >> k);            // first 0 of the run
+                    const int rl = z ? ctz64(z) : 64;
+                    if (rl >= 64 - k) more[ln] = 1;          // run reaches the word's end
+                    len[ln] = rl > 64 - k ? 64 - k : rl;
+                    const int off = d - lit0;                // x - pred_k
+                    dk[ln] = off < 0 ? (uint32_t)(-off) * 2u : (uint32_t)off * 2u + 1u;
+                }
+            }
+        }
+        uint32_t lm = w.ballot(more);
+        while (lm) {
+            const int l = ctz32(lm);
+            lm &= lm - 1u;
+            const int d = dbase + l;
+            const int full = equal_len_coop(w, pv, qi, P0 + d + k, 64 - k);
+            LZ_EACH(w, ln) if (ln == l) len[ln] = full;
+        }
+        const int bl = w.max_i32(len);
+        if (bl > 0) {
+            typename W::template Lanes<uint32_t> kk;
+            LZ_EACH(w, ln) kk[ln] = len[ln] == bl ? dk[ln] : 0xFFFFFFFFu;
+            const uint32_t bk = w.min_u32(kk);
+            if (bl > sl || (bl == sl && bk < skey)) { sl = bl; skey = bk; }
+        }
+    }
+    best_pos = 0;
+    best_len = 0;
+    if (sl > 0) {
+        const int off = (skey & 1u) ? (int)(skey >> 1) : -(int)(skey >> 1);
+        best_len = sl;
+        best_pos = P0 + lit0 + k + off;
+    }
+}
+
+// ---- the whole pair.
+//
+// Three nested granularities:
+//   window (<= 1024 query positions): every lane probes the anchor presence bitmap for its own
+//          32 consecutive positions -> hit masks, one word per lane;
+//   batch  (<= 32 hits of the window, in position order): lane j evaluates hit j on its own
+//          (eval_hit) -- table probe, match length, both approximate extensions -- ahead of
+//          the walk; this is where the lanes do independent work;
+//   walk   : the sequential state machine of parser.cpp:501-708 over chunks of <= 65-msl
+//          positions, consuming the batch records in order.  Without a prediction it jumps
+//          from hit to hit; with one (the mqd positions after a match) it also looks for seeds
+//          along the diagonals of the prediction window.
+// `list` is 32 uint16 of per-warp scratch (shared memory on the device).
+template <class W>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* list)
 {
     ParseState s;
     s.i = 0; s.pred = -1; s.lit = 0;
@@ -418,136 +639,184 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P)
     s.totM = s.totX = s.totN = 0;
     const int Dq = pv.Dq;
     const int n_loop = Dq - P.msl;     // loop runs while i < n_loop (i + msl < Dq, :501)
+    const int NC = 65 - P.msl;         // chunk size: msl-runs starting in the chunk fit 64 bits
+
+    int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
+    int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
+    typename W::template Lanes<uint32_t> hm, r_pos, r_w2, r_w3;
+    typename W::template Lanes<int> r_p;
+    LZ_EACH(w, ln) { hm[ln] = 0; r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; }
 
     while (s.i < n_loop) {
         const int i0 = s.i;
-        int n = n_loop - i0;
-        if (n > 32) n = 32;
-        // positions i0+k with k < nB are in prediction mode (pred >= 0 and lit <= mqd)
-        int nB = 0;
-        if (s.pred >= 0) {
-            nB = P.mqd + 1 - s.lit;
-            if (nB > n) nB = n;
-        }
-        const int lit0 = s.lit;
-        const int P0 = s.pred - s.lit;   // meaningful only when nB > 0
-
-        // (1) anchor presence: lane k tests the mal-mer at i0+k
-        typename W::template Lanes<uint64_t> key;
-        typename W::template Lanes<int> hit;
-        LZ_EACH(w, ln)
-        {
-            hit[ln] = 0;
-            key[ln] = 0;
-            if (ln < n) {
-                uint32_t lo, hi, nm;
-                ext3(pv.q, i0 + ln, lo, hi, nm);
-                if (!(nm & low_mask32(P.mal))) {
-                    key[ln] = kmer_key(lo, hi, P.mal);
-                    const uint32_t b = bitmap_index(key[ln], P.mal, pv.bbits);
-                    hit[ln] = (ld_u32(pv.bitmap + (b >> 5)) >> (b & 31u)) & 1u;
-                }
-            }
-        }
-        uint32_t amask = w.ballot(hit);
-
-        // (2) seed presence along the diagonals of the prediction window
-        uint32_t smask = 0;
-        const int d_lo = -(nB - 1), d_hi = lit0 + P.mrd;   // diagonals [d_lo, d_hi)
-        if (nB > 0) {
-            typename W::template Lanes<uint32_t> sm;
-            LZ_EACH(w, ln) sm[ln] = 0;
-            for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
+        if (i0 >= b_cover) {
+            if (i0 >= win_end) {
+                // ---- new window: lane l probes positions win_base + 32 l + [0, 32)
+                win_base = i0 & ~31;
+                win_end = win_base + 1024 < n_loop ? win_base + 1024 : n_loop;
+                const uint32_t kmask = low_mask32(P.mal);
                 LZ_EACH(w, ln)
                 {
-                    const int d = dbase + ln;
-                    if (d < d_hi) sm[ln] |= (uint32_t)run_starts(diag_equal_bits(pv, i0, P0, d), P.msl);
+                    const int pos0 = win_base + 32 * ln;
+                    uint32_t m = 0;
+                    if (pos0 < win_end) {
+                        const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
+#endif
+                        for (int t = 0; t < 32; ++t) {
+                            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t), nm = funnel_r(a.z, b.z, t);
+                            const bool ok = !(nm & kmask);
+                            const uint32_t bi = ok ? bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits) : 0u;
+                            const uint32_t bit = (ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u)) & (ok ? 1u : 0u);
+                            m |= bit << t;
+                        }
+                        const int nv = win_end - pos0;
+                        if (nv < 32) m &= low_mask32(nv);
+                    }
+                    hm[ln] = m;
                 }
             }
-            smask = w.or_u32(sm) & low_mask32(nB);
+            // ---- new batch: the first <= 32 hits at or after i0
+            typename W::template Lanes<uint32_t> mm;
+            typename W::template Lanes<int> cnt, pre;
+            LZ_EACH(w, ln)
+            {
+                const int rel = i0 - (win_base + 32 * ln);
+                uint32_t m = hm[ln];
+                if (rel >= 32) m = 0;
+                else if (rel > 0) m &= ~low_mask32(rel);
+                mm[ln] = m;
+                cnt[ln] = popc32(m);
+            }
+            w.exscan_add(pre, cnt);
+            const int total = w.add_i32(cnt);
+            LZ_EACH(w, ln)
+            {
+                uint32_t m = mm[ln];
+                int idx = pre[ln];
+                while (m && idx < 32) {
+                    list[idx++] = (uint16_t)(32 * ln + ctz32(m));
+                    m &= m - 1u;
+                }
+            }
+            w.sync();
+            const int b_cnt = total < 32 ? total : 32;
+            LZ_EACH(w, ln) r_p[ln] = ln < b_cnt ? win_base + (int)list[ln] : 0x7FFFFFFF;
+            w.sync();
+            b_cover = total <= 32 ? win_end : w.get(r_p, 31) + 1;
+            LZ_EACH(w, ln)
+            {
+                uint32_t a = 0, b = 0, c = 0;
+                if (ln < b_cnt) eval_hit(pv, P, r_p[ln], a, b, c);
+                r_pos[ln] = a; r_w2[ln] = b; r_w3[ln] = c;
+            }
         }
 
-        // (3) walk the candidate positions in order; the first real match ends the step
-        uint32_t cand = amask | smask;
-        bool matched = false;
-        while (cand) {
-            const int k = ctz32(cand);
-            cand &= cand - 1u;
-            const int qi = i0 + k;
-            const bool modeB = k < nB;
-            int best_pos = 0, best_len = 0;
-            if (modeB && ((smask >> k) & 1u)) {
-                // best seed at k: longest; ties -> closest to the prediction, then smallest position
-                int sl = 0;
-                uint32_t skey = 0xFFFFFFFFu;
-                for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
-                    typename W::template Lanes<int> len, more;
-                    typename W::template Lanes<uint32_t> dk;
-                    LZ_EACH(w, ln)
-                    {
-                        const int d = dbase + ln;
-                        len[ln] = 0;
-                        more[ln] = 0;
-                        dk[ln] = 0xFFFFFFFFu;
-                        if (d < d_hi) {
-                            const uint64_t E = diag_equal_bits(pv, i0, P0, d);
-                            if ((run_starts(E, P.msl) >> k) & 1ull) {
-                                const uint64_t z = ~(E >> k);            // first 0 of the run
-                                const int rl = z ? ctz64(z) : 64;
-                                if (rl >= 64 - k) more[ln] = 1;          // run reaches the word's end
-                                len[ln] = rl > 64 - k ? 64 - k : rl;
-                                const int off = d - lit0;                // x - pred_k
-                                dk[ln] = off < 0 ? (uint32_t)(-off) * 2u : (uint32_t)off * 2u + 1u;
-                            }
-                        }
-                    }
-                    uint32_t lm = w.ballot(more);
-                    while (lm) {
-                        const int l = ctz32(lm);
-                        lm &= lm - 1u;
-                        const int d = dbase + l;
-                        const int full = equal_len_coop(w, pv, qi, P0 + d + k, 64 - k);
-                        LZ_EACH(w, ln) if (ln == l) len[ln] = full;
-                    }
-                    const int bl = w.max_i32(len);
-                    if (bl > 0) {
-                        typename W::template Lanes<uint32_t> kk;
-                        LZ_EACH(w, ln) kk[ln] = len[ln] == bl ? dk[ln] : 0xFFFFFFFFu;
-                        const uint32_t bk = w.min_u32(kk);
-                        if (bl > sl || (bl == sl && bk < skey)) { sl = bl; skey = bk; }
-                    }
-                }
-                if (sl > 0) {
-                    const int off = (skey & 1u) ? (int)(skey >> 1) : -(int)(skey >> 1);
-                    best_len = sl;
-                    best_pos = P0 + lit0 + k + off;
-                }
+        if (s.pred < 0) {
+            // ---- no prediction (:507-532): the next event is the next live anchor record
+            typename W::template Lanes<int> c;
+            LZ_EACH(w, ln) c[ln] = r_p[ln] >= i0 && (r_w2[ln] & HIT_LIVE);
+            const uint32_t vm = w.ballot(c);
+            if (!vm) {
+                s.lit += b_cover - i0;
+                s.i = b_cover;
+                continue;
             }
-            int a_pos = 0, a_len = 0;
-            if ((amask >> k) & 1u) anchor_lookup(w, pv, P, qi, w.get(key, k), a_pos, a_len);
-            if (!modeB) {
-                best_pos = a_pos;                     // :507-532 (a hit at position 0 counts here)
-                best_len = a_len;
-            } else if (a_pos) {                       // :604 (position 0 == "none")
-                if (!best_pos) { best_pos = a_pos; best_len = a_len; }
-                else {
-                    const double pa = ipow_u32(one_minus_4pow(a_len), (uint32_t)(2 * (pv.Dr + 1 - a_len)));
-                    const double pc = ipow_u32(one_minus_4pow(best_len), (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
-                    if (pa > pc) { best_pos = a_pos; best_len = a_len; }
+            const int j = ctz32(vm);
+            const int qi = w.get(r_p, j);
+            uint32_t w2 = w.get(r_w2, j), w3 = w.get(r_w3, j);
+            int a_pos = (int)w.get(r_pos, j), a_len = (int)(w2 & 63u);
+            if (w2 & HIT_DEFER) {
+                uint32_t lo, hi, nm;
+                ext3(pv.q, qi, lo, hi, nm);
+                anchor_lookup(w, pv, P, qi, kmer_key(lo, hi, P.mal), a_pos, a_len);
+                w2 = 0;
+            }
+            if (a_len > 0 && a_len >= P.msl) take_match(w, pv, P, s, qi, s.lit + (qi - i0), -1, a_pos, a_len, w2, w3);
+            else {
+                s.lit += qi + 1 - i0;
+                s.i = qi + 1;
+            }
+            continue;
+        }
+
+        // ---- prediction mode (:533-624): pred >= 0 and lit <= mqd
+        const int lit0 = s.lit;
+        const int P0 = s.pred - s.lit;
+        int n = P.mqd + 1 - lit0;
+        if (n > NC) n = NC;
+        if (n > b_cover - i0) n = b_cover - i0;
+        // the first anchor record inside the chunk that counts here (position 0 == "none", :604)
+        typename W::template Lanes<int> c;
+        LZ_EACH(w, ln)
+            c[ln] = r_p[ln] >= i0 && r_p[ln] < i0 + n && (r_w2[ln] & HIT_LIVE) && ((r_w2[ln] & HIT_DEFER) || r_pos[ln] != 0u);
+        const uint32_t vm = w.ballot(c);
+        const int ja = vm ? ctz32(vm) : -1;
+        const int ka = ja >= 0 ? w.get(r_p, ja) - i0 : n;
+        const int ns = ja >= 0 ? ka + 1 : n;          // positions examined by this step
+
+        // seeds: runs of >= msl equal bases along the diagonals [d_lo, d_hi) of the window
+        const Planes64 Q = ext64(pv.q, i0);
+        const int d_lo = -(ns - 1), d_hi = lit0 + P.mrd;
+        typename W::template Lanes<uint64_t> sm;
+        LZ_EACH(w, ln) sm[ln] = 0;
+        for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
+            LZ_EACH(w, ln)
+            {
+                const int d = dbase + ln;
+                if (d < d_hi) sm[ln] |= run_starts(diag_equal64(pv, Q, i0, P0, d), P.msl);
+            }
+        }
+        uint64_t cand = w.or_u64(sm) & low_mask64(ns);
+
+        bool matched = false;
+        for (;;) {
+            const int ks = cand ? ctz64(cand) : 64;
+            const int k = ks < ka ? ks : ka;
+            if (k >= ns) break;
+            const int qi = i0 + k;
+            int best_pos = 0, best_len = 0;
+            if (ks == k) {
+                best_seed(w, pv, P, Q, i0, P0, lit0, k, d_lo, d_hi, best_pos, best_len);
+                cand &= cand - 1ull;
+            }
+            uint32_t w2 = 0, w3 = 0;
+            if (ja >= 0 && k == ka) {
+                w2 = w.get(r_w2, ja);
+                w3 = w.get(r_w3, ja);
+                int a_pos = (int)w.get(r_pos, ja), a_len = (int)(w2 & 63u);
+                if (w2 & HIT_DEFER) {
+                    uint32_t lo, hi, nm;
+                    ext3(pv.q, qi, lo, hi, nm);
+                    anchor_lookup(w, pv, P, qi, kmer_key(lo, hi, P.mal), a_pos, a_len);
+                    w2 = 0;
                 }
+                bool take_anchor = false;
+                if (a_pos) {                              // :604
+                    if (!best_pos) take_anchor = true;    // :606-610
+                    else {
+                        const double pa = ipow_u32(one_minus_4pow(a_len), (uint32_t)(2 * (pv.Dr + 1 - a_len)));
+                        const double pc = ipow_u32(one_minus_4pow(best_len), (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
+                        take_anchor = pa > pc;
+                    }
+                }
+                if (take_anchor) { best_pos = a_pos; best_len = a_len; }
+                else w2 = 0;
             }
             if (best_len >= P.msl) {
-                take_match(w, pv, P, s, qi, lit0 + k, modeB ? P0 + lit0 + k : -1, best_pos, best_len);
+                take_match(w, pv, P, s, qi, lit0 + k, P0 + lit0 + k, best_pos, best_len, w2, w3);
                 matched = true;
                 break;
             }
+            if (ja >= 0 && k == ka) break;       // the step ends at the anchor's position
         }
         if (!matched) {
-            // n literal steps (:699-707)
-            s.i = i0 + n;
-            s.lit = lit0 + n;
-            if (s.pred >= 0) s.pred = s.lit > P.mqd ? -1 : s.pred + n;
-        } else if (s.lit > P.mqd) s.pred = -1;       // (:706 after a match: lit is 0, never true)
+            // ns literal steps (:699-707)
+            s.i = i0 + ns;
+            s.lit = lit0 + ns;
+            s.pred = s.lit > P.mqd ? -1 : s.pred + ns;
+        }
     }
 
     // tail (:710-713): with a live prediction the rest is compared against the reference shifted

@@ -48,6 +48,14 @@ LZ_HD int ctz64(uint64_t x)  // x != 0
     return __builtin_ctzll(x);
 #endif
 }
+LZ_HD int popc64(uint64_t x)
+{
+#if defined(__CUDA_ARCH__)
+    return __popcll(x);
+#else
+    return __builtin_popcountll(x);
+#endif
+}
 LZ_HD int clz32(uint32_t x)  // x != 0
 {
 #if defined(__CUDA_ARCH__)
@@ -107,6 +115,14 @@ struct DevWarp {
     __device__ __forceinline__ int add_i32(const Lanes<int>& x) const { return __reduce_add_sync(0xFFFFFFFFu, x.v); }
     __device__ __forceinline__ uint32_t min_u32(const Lanes<uint32_t>& x) const { return __reduce_min_sync(0xFFFFFFFFu, x.v); }
     __device__ __forceinline__ uint32_t or_u32(const Lanes<uint32_t>& x) const { return __reduce_or_sync(0xFFFFFFFFu, x.v); }
+    __device__ __forceinline__ uint64_t or_u64(const Lanes<uint64_t>& x) const
+    {
+        const uint32_t lo = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)x.v);
+        const uint32_t hi = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)(x.v >> 32));
+        return ((uint64_t)hi << 32) | lo;
+    }
+    // orders this warp's shared-memory scratch writes before its later reads
+    __device__ __forceinline__ void sync() const { __syncwarp(); }
     // value of lane `src` (uniform src)
     template <class T>
     __device__ __forceinline__ T get(const Lanes<T>& x, int src) const { return __shfl_sync(0xFFFFFFFFu, x.v, src); }
@@ -161,6 +177,8 @@ struct HostWarp {
     int add_i32(const Lanes<int>& x) const { int r = 0; for (int l = 0; l < 32; ++l) r += x.v[l]; return r; }
     uint32_t min_u32(const Lanes<uint32_t>& x) const { uint32_t r = x.v[0]; for (int l = 1; l < 32; ++l) r = x.v[l] < r ? x.v[l] : r; return r; }
     uint32_t or_u32(const Lanes<uint32_t>& x) const { uint32_t r = 0; for (int l = 0; l < 32; ++l) r |= x.v[l]; return r; }
+    uint64_t or_u64(const Lanes<uint64_t>& x) const { uint64_t r = 0; for (int l = 0; l < 32; ++l) r |= x.v[l]; return r; }
+    void sync() const {}
     template <class T>
     T get(const Lanes<T>& x, int src) const { return x.v[src & 31]; }
     template <class T>

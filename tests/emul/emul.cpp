@@ -78,6 +78,7 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
     std::atomic<uint64_t> next{0};
     auto worker = [&]() {
         HostWarp w;
+        uint16_t list[32];
         HostIndex ix;
         for (;;) {
             uint64_t j = next.fetch_add(1);
@@ -92,7 +93,7 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 pv.r = seqs[r].r.data(); pv.Dr = r_form_len(seqs[r].len, P.mrd);
                 pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
                 pv.table = ix.table.data(); pv.tbits = ix.tbits;
-                PairResult res = parse_pair(w, pv, P);
+                PairResult res = parse_pair(w, pv, P, list);
                 out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
                 ++k;
             };
