@@ -136,7 +136,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     LZ_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto& ev : c->ev) LZ_CUDA(c, cudaEventCreate(&ev));
     LZ_CUDA(c, cudaMalloc((void**)&c->d_counter, sizeof(unsigned long long)));
-    c->blocks_per_sm = parse_blocks_per_sm();
+    c->blocks_per_sm = parse_blocks_per_sm(c->P);
     return LZANI_OK;
 }
 

@@ -80,11 +80,12 @@ k_build_index(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 // K3.  Persistent warps pull pair numbers from a global counter.  Pair k (relative to the
 // batch's first pair) belongs to the batch row found in row_off; its query is q_ids[k] or, for
 // the dense all2all list, the (k - row_off[row])-th id different from the reference.
+template <class PT>
 __global__ void __launch_bounds__(LZ_PARSE_THREADS)
 k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
               const uint32_t* __restrict__ row_ref, const RefIndex* __restrict__ row_idx,
               const uint64_t* __restrict__ row_off, uint32_t n_rows, const uint32_t* __restrict__ q_ids,
-              uint64_t pair_begin, uint64_t pair_end, Prm P, const uint32_t* __restrict__ bitmap_pool,
+              uint64_t pair_begin, uint64_t pair_end, PT P, const uint32_t* __restrict__ bitmap_pool,
               const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
               int3* __restrict__ out)
 {
@@ -141,11 +142,13 @@ cudaError_t launch_build_index(cudaStream_t st, const Rec* recs, const SeqMeta* 
     return cudaGetLastError();
 }
 
-int parse_blocks_per_sm()
+int parse_blocks_per_sm(const Prm& P)
 {
     int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_parse_pairs, LZ_PARSE_THREADS, 0) != cudaSuccess || nb < 1)
-        nb = 1;
+    const cudaError_t e = is_default_kernel_params(P)
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_parse_pairs<PrmDefault>, LZ_PARSE_THREADS, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_parse_pairs<Prm>, LZ_PARSE_THREADS, 0);
+    if (e != cudaSuccess || nb < 1) nb = 1;
     return nb;
 }
 
@@ -156,9 +159,15 @@ cudaError_t launch_parse(cudaStream_t st, int grid_blocks, const Rec* recs, cons
                          unsigned long long* counter, void* out)
 {
     if (pair_end <= pair_begin) return cudaSuccess;
-    k_parse_pairs<<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(recs, meta, row_ref, row_idx, row_off, n_rows, q_ids,
-                                                         pair_begin, pair_end, P, bitmap_pool, table_pool,
-                                                         counter, reinterpret_cast<int3*>(out));
+    if (is_default_kernel_params(P)) {
+        const PrmDefault D{P.mrd, P.mqd, P.reg};
+        k_parse_pairs<PrmDefault><<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(recs, meta, row_ref, row_idx, row_off, n_rows,
+                                                                        q_ids, pair_begin, pair_end, D, bitmap_pool,
+                                                                        table_pool, counter, reinterpret_cast<int3*>(out));
+    } else
+        k_parse_pairs<Prm><<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(recs, meta, row_ref, row_idx, row_off, n_rows, q_ids,
+                                                                 pair_begin, pair_end, P, bitmap_pool, table_pool,
+                                                                 counter, reinterpret_cast<int3*>(out));
     return cudaGetLastError();
 }
 

@@ -16,7 +16,7 @@ cudaError_t launch_build_index(cudaStream_t st, const Rec* recs, const SeqMeta* 
                                const RefIndex* row_idx, const uint32_t* blk_base, uint32_t n_rows,
                                uint32_t n_blocks, const Prm& P, uint32_t* bitmap_pool, uint64_t* table_pool);
 
-int parse_blocks_per_sm();
+int parse_blocks_per_sm(const Prm& P);
 
 cudaError_t launch_parse(cudaStream_t st, int grid_blocks, const Rec* recs, const SeqMeta* meta,
                          const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,

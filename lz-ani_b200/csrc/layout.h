@@ -40,6 +40,14 @@ constexpr uint64_t LZ_EMPTY = ~0ull;
 struct Rec { uint32_t x, y, z, w; };   // same layout as uint4
 
 struct Prm { int mal, msl, mrd, mqd, reg, aw, am, ar; };
+// The reference's default k-mer / extension parameters (params.h:38-45) as compile-time
+// constants: the parse kernel is instantiated once for them (bit loops unroll, masks fold) and
+// once for arbitrary run-time values (Prm).  The kernel code only says P.mal, P.msl, ...
+struct PrmDefault {
+    static constexpr int mal = 11, msl = 7, aw = 15, am = 7, ar = 3;
+    int mrd, mqd, reg;
+};
+LZ_HD bool is_default_kernel_params(const Prm& p) { return p.mal == 11 && p.msl == 7 && p.aw == 15 && p.am == 7 && p.ar == 3; }
 
 // per-sequence placement in the record pool
 struct SeqMeta {

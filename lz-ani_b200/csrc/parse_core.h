@@ -99,10 +99,20 @@ struct BwdStream {   // position k <-> q[qe-1-k] vs r[re-1-k]
     }
 };
 
+struct AnyStream {   // direction chosen at run time: one instantiation of approx_extend()
+    const PairView* pv; int a, b; bool back;
+    LZ_HD uint32_t word(int wi) const
+    {
+        if (back) { BwdStream s{pv, a, b}; return s.word(wi); }
+        FwdStream s{pv, a, b};
+        return s.word(wi);
+    }
+};
+
 // ---- equal_len (parser.cpp:192-207): common prefix of q[qpos..] and r[rpos..], the first
 // `from` bases being known equal.  Uniform arguments, uniform result.
 template <class W>
-LZ_HD int equal_len_coop(W& w, const PairView& pv, int qpos, int rpos, int from)
+LZ_COLD int equal_len_coop(W& w, const PairView& pv, int qpos, int rpos, int from)
 {
     // first word by every lane alike (one broadcast load); most matches end inside it
     const uint32_t w0 = mism32(pv.q, pv.Dq, qpos + from, pv.r, pv.Dr, rpos + from);
@@ -134,8 +144,8 @@ LZ_HD int equal_len_coop(W& w, const PairView& pv, int qpos, int rpos, int from)
 // overflow is a min-reduction, the last run end a max-reduction.  Also returns the number of
 // matching positions below the returned length (what compare_ranges, parser.cpp:210-248, would
 // emit as match factors).  Requires aw <= 32 and ar <= 32 (checked by the host).
-template <class W, class S>
-LZ_HD void approx_extend(W& w, const S& st, int limit, const Prm& P, int& out_len, int& out_matches)
+template <class W, class PT>
+LZ_COLD void approx_extend(W& w, const AnyStream& st, int limit, const PT& P, int& out_len, int& out_matches)
 {
     out_len = 0;
     out_matches = 0;
@@ -159,10 +169,11 @@ LZ_HD void approx_extend(W& w, const S& st, int limit, const Prm& P, int& out_le
             int f = 0x7FFFFFFF;
             // cheap bound: the window around any position of this word is inside these bits
             if (p0 < limit && popc32(cur[ln]) + popc32(prev[ln] >> (33 - P.aw > 31 ? 31 : 33 - P.aw)) > P.am) {
-                for (int j = 0; j < 32; ++j) {
-                    const uint64_t win = (x >> (33 + j - P.aw)) & wmask;
-                    const int c = popc32((uint32_t)win) + popc32((uint32_t)(win >> 32));
-                    if (c > P.am) { f = p0 + j; break; }
+                uint32_t t = cur[ln];                 // the window can only overflow at a mismatch
+                while (t) {
+                    const int j = ctz32(t);
+                    if (popc64((x >> (33 + j - P.aw)) & wmask) > P.am) { f = p0 + j; break; }
+                    t &= t - 1u;
                 }
             }
             fb[ln] = f;
@@ -208,7 +219,7 @@ LZ_HD void approx_extend(W& w, const S& st, int limit, const Prm& P, int& out_le
 // the reference continuing from r_left and, after it, against the reference ENDING at r_right
 // (the caller passes the end of the new match, parser.cpp:632 -- kept).  len <= 1024.
 template <class W>
-LZ_HD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_right, int len)
+LZ_COLD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_right, int len)
 {
     if (len <= 0) return 0;
     const int q0 = qe - len;
@@ -265,8 +276,8 @@ LZ_HD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_rig
 // longest common prefix over all reference positions whose mal-mer equals the query's at
 // qpos; ties -> smallest position (the reference's strict '>' over ascending positions).
 // (0,0) when there is none.  32 slots of the chain are inspected per step, one per lane.
-template <class W>
-LZ_HD void anchor_lookup(W& w, const PairView& pv, const Prm& P, int qpos, uint64_t key, int& a_pos, int& a_len)
+template <class W, class PT>
+LZ_COLD void anchor_lookup(W& w, const PairView& pv, const PT& P, int qpos, uint64_t key, int& a_pos, int& a_len)
 {
     a_pos = 0;
     a_len = 0;
@@ -391,7 +402,8 @@ LZ_HD uint64_t diag_equal64(const PairView& pv, const Planes64& Q, int i0, int P
 // (try_extend_forward/backward, parser.cpp:377-441).  `examined` = positions the sequential
 // walk would have looked at; complete == false when the walk would run on into the next word.
 struct ExtWord { int len, matches, examined; bool complete; };
-LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const Prm& P)
+template <class PT>
+LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const PT& P)
 {
     ExtWord o;
     o.len = 0; o.matches = 0; o.examined = 0; o.complete = true;
@@ -441,7 +453,8 @@ constexpr uint32_t HIT_FWD = 1u << 20;     // fwd fields valid
 constexpr uint32_t HIT_BWD = 1u << 21;     // bwd fields valid
 constexpr int HIT_MAX_CHAIN = 6;           // matching-tag slots one lane inspects before deferring
 
-LZ_HD void eval_hit(const PairView& pv, const Prm& P, int p, uint32_t& o_pos, uint32_t& o_w2, uint32_t& o_w3)
+template <class PT>
+LZ_HD void eval_hit(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uint32_t& o_w2, uint32_t& o_w3)
 {
     o_pos = 0; o_w2 = 0; o_w3 = 0;
     uint32_t lo, hi, nm;
@@ -502,8 +515,8 @@ struct ParseState {
 
 // One match found at query position qi (parser.cpp:626-698), counts only.  (w2, w3) is the
 // speculative record of eval_hit() when the match IS that anchor, else w2 == 0.
-template <class W>
-LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int qi, int lit_k, int pred_k,
+template <class W, class PT>
+LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int qi, int lit_k, int pred_k,
                       int best_pos, int best_len, uint32_t w2, uint32_t w3)
 {
     int dist = best_pos - pred_k;
@@ -533,7 +546,7 @@ LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int
                 back = (int)(w3 & 63u);
                 bm = (int)((w3 >> 6) & 63u);
             } else {
-                BwdStream bs{&pv, qi, best_pos};
+                AnyStream bs{&pv, qi, best_pos, true};
                 approx_extend(w, bs, lim, P, back, bm);
             }
         }
@@ -550,7 +563,7 @@ LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int
     } else {
         int lim = pv.Dq - qn;
         if (pv.Dr - pn < lim) lim = pv.Dr - pn;
-        FwdStream fs{&pv, qn, pn};
+        AnyStream fs{&pv, qn, pn, false};
         approx_extend(w, fs, lim, P, fwd, fm);      // :691-695
     }
     s.curM += fm;
@@ -563,8 +576,8 @@ LZ_HD void take_match(W& w, const PairView& pv, const Prm& P, ParseState& s, int
 
 // best seed at chunk position k (parser.cpp:548-580): longest; ties -> closest to the
 // prediction, then smallest position.  Lanes own diagonals.
-template <class W>
-LZ_HD void best_seed(W& w, const PairView& pv, const Prm& P, const Planes64& Q, int i0, int P0, int lit0, int k,
+template <class W, class PT>
+LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q, int i0, int P0, int lit0, int k,
                      int d_lo, int d_hi, int& best_pos, int& best_len)
 {
     int sl = 0;
@@ -629,8 +642,8 @@ LZ_HD void best_seed(W& w, const PairView& pv, const Prm& P, const Planes64& Q, 
 //          from hit to hit; with one (the mqd positions after a match) it also looks for seeds
 //          along the diagonals of the prediction window.
 // `list` is 32 uint16 of per-warp scratch (shared memory on the device).
-template <class W>
-LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* list)
+template <class W, class PT>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* list)
 {
     ParseState s;
     s.i = 0; s.pred = -1; s.lit = 0;
@@ -649,6 +662,10 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* li
 
     while (s.i < n_loop) {
         const int i0 = s.i;
+        // the match this step finds, if any (one take_match call site keeps the code small)
+        bool matched = false;
+        int m_qi = 0, m_lit = 0, m_pred = -1, m_pos = 0, m_len = 0;
+        uint32_t m_w2 = 0, m_w3 = 0;
         if (i0 >= b_cover) {
             if (i0 >= win_end) {
                 // ---- new window: lane l probes positions win_base + 32 l + [0, 32)
@@ -733,14 +750,14 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* li
                 anchor_lookup(w, pv, P, qi, kmer_key(lo, hi, P.mal), a_pos, a_len);
                 w2 = 0;
             }
-            if (a_len > 0 && a_len >= P.msl) take_match(w, pv, P, s, qi, s.lit + (qi - i0), -1, a_pos, a_len, w2, w3);
-            else {
+            if (a_len > 0 && a_len >= P.msl) {
+                matched = true;
+                m_qi = qi; m_lit = s.lit + (qi - i0); m_pred = -1; m_pos = a_pos; m_len = a_len; m_w2 = w2; m_w3 = w3;
+            } else {
                 s.lit += qi + 1 - i0;
                 s.i = qi + 1;
             }
-            continue;
-        }
-
+        } else {
         // ---- prediction mode (:533-624): pred >= 0 and lit <= mqd
         const int lit0 = s.lit;
         const int P0 = s.pred - s.lit;
@@ -770,7 +787,6 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* li
         }
         uint64_t cand = w.or_u64(sm) & low_mask64(ns);
 
-        bool matched = false;
         for (;;) {
             const int ks = cand ? ctz64(cand) : 64;
             const int k = ks < ka ? ks : ka;
@@ -805,8 +821,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* li
                 else w2 = 0;
             }
             if (best_len >= P.msl) {
-                take_match(w, pv, P, s, qi, lit0 + k, P0 + lit0 + k, best_pos, best_len, w2, w3);
                 matched = true;
+                m_qi = qi; m_lit = lit0 + k; m_pred = P0 + lit0 + k; m_pos = best_pos; m_len = best_len; m_w2 = w2; m_w3 = w3;
                 break;
             }
             if (ja >= 0 && k == ka) break;       // the step ends at the anchor's position
@@ -817,6 +833,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const Prm& P, uint16_t* li
             s.lit = lit0 + ns;
             s.pred = s.lit > P.mqd ? -1 : s.pred + ns;
         }
+        }
+        if (matched) take_match(w, pv, P, s, m_qi, m_lit, m_pred, m_pos, m_len, m_w2, m_w3);
     }
 
     // tail (:710-713): with a live prediction the rest is compared against the reference shifted

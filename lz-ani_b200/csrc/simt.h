@@ -16,9 +16,13 @@
 #if defined(__CUDACC__)
 #define LZ_HD __host__ __device__ __forceinline__
 #define LZ_D __device__ __forceinline__
+// rarely executed warp-cooperative routines: kept out of line so that the hot loop of the
+// parse kernel stays inside the instruction cache
+#define LZ_COLD __host__ __device__ __noinline__
 #else
 #define LZ_HD inline
 #define LZ_D inline
+#define LZ_COLD inline
 #endif
 
 namespace lzani {

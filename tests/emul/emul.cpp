@@ -93,7 +93,10 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 pv.r = seqs[r].r.data(); pv.Dr = r_form_len(seqs[r].len, P.mrd);
                 pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
                 pv.table = ix.table.data(); pv.tbits = ix.tbits;
-                PairResult res = parse_pair(w, pv, P, list);
+                // same dispatch as launch_parse(): compile-time defaults or run-time parameters
+                PairResult res;
+                if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, list); }
+                else res = parse_pair(w, pv, P, list);
                 out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
                 ++k;
             };
