@@ -1,0 +1,87 @@
+"""CLI-level drop-in test: the reference's own host program (CLI, loader, filter, reorder, TSV
+writers -- compiled unmodified by integration/Makefile) with CLZMatcher::do_matching replaced by
+the B200 library must write TSV files byte-identical to the reference's
+(reference CI: `cmp ani.tsv test/vir61.ani.tsv`, .github/workflows/main.yml:65-66).
+
+The golden TSVs in tests/golden/*.ani.tsv.gz come from the unmodified reference CLI
+(tests/golden/make_golden_tsv.py)."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import make_golden as mg
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+CLI = os.path.join(ROOT, "integration", "_build", "lz-ani-b200")
+ALT = "--mal 15 --msl 9 --mrd 60 --mqd 60 --reg 60 --aw 20 --am 9 --ar 4".split()
+LETTERS = np.frombuffer(b"ACGTNN", dtype=np.uint8)
+
+
+def write_fasta(path, ss, order=None):
+    ids = range(len(ss)) if order is None else order
+    with open(path, "wb") as f:
+        for i in ids:
+            f.write(b">" + ss.names[i].encode() + b" synthetic description\n")
+            s = LETTERS[ss.codes[i]].tobytes()
+            for o in range(0, len(s), 70):
+                f.write(s[o:o + 70] + b"\n")
+
+
+def golden(name):
+    return (gzip.open(os.path.join(GOLD, name + ".ani.tsv.gz")).read(),
+            gzip.open(os.path.join(GOLD, name + ".ani.ids.tsv.gz")).read())
+
+
+def need_cli():
+    if not os.path.exists(CLI):
+        pytest.skip("integration/_build/lz-ani-b200 not built (needs /root/reference at build time)")
+
+
+def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
+    need_cli()
+    syms = subprocess.run(["nm", "-C", CLI], capture_output=True, text=True).stdout
+    assert "CParser::parse" not in syms and "CParser::prepare_reference" not in syms
+    assert "lzani_run_rows" in syms
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present")
+    except ImportError:
+        pass
+    ss = mg.get_set("example")
+    write_fasta(tmp_path / "in.fna", ss)
+    r = subprocess.run([CLI, "all2all", "--in-fasta", str(tmp_path / "in.fna"), "--out", str(tmp_path / "o.tsv"), "-V", "1"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU fallback" in r.stderr
+    assert not os.path.exists(tmp_path / "o.tsv") or os.path.getsize(tmp_path / "o.tsv") == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,setname,extra", [
+    ("vir61_default", "vir61", []),
+    ("vir61_alt_complete", "vir61", ALT + ["--out-format", "complete"]),
+    ("example_default", "example", []),
+    ("example_filter09", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9"]),
+])
+def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
+    need_cli()
+    ss = mg.get_set(setname)
+    order = None
+    if "--flt-kmerdb" in extra:
+        # the filter's header lists the names in the original FASTA order (lz_matcher.cpp:43-75)
+        hdr = open(os.path.join(GOLD, "example_fltr.txt")).readline().rstrip("\n").split(",")[1:]
+        hdr = [h for h in hdr if h]
+        order = [ss.names.index(h) for h in hdr]
+    fa = tmp_path / "in.fna"
+    write_fasta(fa, ss, order)
+    out = tmp_path / "ani.tsv"
+    r = subprocess.run([CLI, "all2all", "--in-fasta", str(fa), "--out", str(out), "-V", "1"] + extra,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want_tsv, want_ids = golden(case)
+    assert open(out, "rb").read() == want_tsv
+    assert open(str(out).replace("ani.tsv", "ani.ids.tsv"), "rb").read() == want_ids
