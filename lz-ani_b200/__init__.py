@@ -21,7 +21,7 @@ import subprocess
 
 import numpy as np
 
-from . import hostio, synth  # noqa: F401
+from . import hostio, sharding, synth  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
@@ -176,8 +176,4 @@ class Matcher:
         return out
 
 
-def shard_rows(n_refs: int, rank: int, world: int) -> np.ndarray:
-    """Reference rows of one rank: r mod world == rank over the length-descending ids, so every
-    rank gets the same length mix (the reference's task unit is one reference row,
-    lz_matcher.cpp:200-209)."""
-    return np.arange(rank, n_refs, world, dtype=np.uint32)
+from .sharding import shard_rows  # noqa: E402,F401
