@@ -39,12 +39,16 @@ constexpr uint64_t LZ_EMPTY = ~0ull;
 
 struct Rec { uint32_t x, y, z, w; };   // same layout as uint4
 
-struct Prm { int mal, msl, mrd, mqd, reg, aw, am, ar; };
+struct Prm {
+    int mal, msl, mrd, mqd, reg, aw, am, ar;
+    static constexpr bool kSpecSeeds = false;   // speculative per-hit seed scan: msl == 7 kernels only
+};
 // The reference's default k-mer / extension parameters (params.h:38-45) as compile-time
 // constants: the parse kernel is instantiated once for them (bit loops unroll, masks fold) and
 // once for arbitrary run-time values (Prm).  The kernel code only says P.mal, P.msl, ...
 struct PrmDefault {
     static constexpr int mal = 11, msl = 7, aw = 15, am = 7, ar = 3;
+    static constexpr bool kSpecSeeds = true;
     int mrd, mqd, reg;
 };
 LZ_HD bool is_default_kernel_params(const Prm& p) { return p.mal == 11 && p.msl == 7 && p.aw == 15 && p.am == 7 && p.ar == 3; }
@@ -76,12 +80,16 @@ LZ_HD int ceil_log2_u64(uint64_t v)
     while (((uint64_t)1 << b) < v) ++b;
     return b;
 }
-// bitmap: exact (direct-addressed) when the key space is small enough, else ~1/32 occupancy
+// bitmap: exact (direct-addressed, 4^mal bits) whenever the key space is at most 2^24 bits (2 MiB;
+// 512 KiB for the default mal = 11) -- a compile-time fact for the default-parameter kernel --
+// else hashed at ~1/32 occupancy
+constexpr int LZ_DIRECT_BITMAP_MAX_BITS = 24;
 LZ_HD uint32_t index_bbits(int Dr, int mal)
 {
+    if (2 * mal <= LZ_DIRECT_BITMAP_MAX_BITS) return (uint32_t)(2 * mal);
     int want = ceil_log2_u64((uint64_t)(Dr > 1 ? Dr : 2)) + 5;
     if (want < 10) want = 10;
-    return (uint32_t)(2 * mal <= want ? 2 * mal : want);
+    return (uint32_t)want;
 }
 // table: load factor <= 0.4
 LZ_HD uint32_t index_tbits(int Dr)
@@ -132,7 +140,7 @@ LZ_HD uint64_t mix64(uint64_t key, uint64_t mul) { return key * mul; }
 
 LZ_HD uint32_t bitmap_index(uint64_t key, int mal, uint32_t bbits)
 {
-    if ((uint32_t)(2 * mal) <= bbits) return (uint32_t)key;
+    if (2 * mal <= LZ_DIRECT_BITMAP_MAX_BITS) return (uint32_t)key;     // bbits == 2*mal (index_bbits)
     return (uint32_t)(mix64(key, 0xD6E8FEB86659FD93ull) >> (64 - bbits));
 }
 LZ_HD uint32_t table_home(uint64_t key, uint32_t tbits)

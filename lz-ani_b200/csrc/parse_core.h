@@ -437,6 +437,89 @@ LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const PT& P)
 }
 
 // ------------------------------------------------------------------------------------------
+// Speculative seed scan, evaluated by ONE lane for ITS hit ahead of the walk (msl == 7 kernels).
+// Should the walk take the hit's anchor as a match (with the forward extension of its record),
+// it continues in prediction mode at query position i0, reference position P0, literal run 0.
+// The seeds of the next positions k = 0..K (parser.cpp:548-580: reference positions
+// x in [P0, P0+k+mrd) whose msl-mer equals the query's at i0+k) then depend on nothing else, so
+// the first k that has one can be found now.  Row-wise bit-parallel: for query base m the mismatch
+// mask Mis_m of the 96-base reference window against that base; a seed at (k, x) is a 0 bit x of
+//   S_k = Mis_k | Mis_{k+1}>>1 | ... | Mis_{k+6}>>6   (built by doubling: pairs, fours, 4+3).
+// Returns the first k with a seed, 64 when there is none in [0, K], -1 when not applicable (an N
+// or the sequence end inside the window: left to the warp-cooperative path).
+struct V3 { uint32_t a, b, c; };
+LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 32
+{
+    V3 r;
+    r.a = x.a | funnel_r(y.a, y.b, j);
+    r.b = x.b | funnel_r(y.b, y.c, j);
+    r.c = x.c | (y.c >> j);
+    return r;
+}
+constexpr int SPEC_MAX_K = 57;
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0;   // TEST ONLY counters (tests/emul)
+#endif
+template <class PT>
+LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
+{
+    // window: query bases [i0, i0+K+7), reference bases [P0, P0+K+mrd+6)
+    if (K < 0 || K > SPEC_MAX_K || K + P.mrd + 6 > 96 || P0 < 0) return -1;
+    const Planes64 Q = ext64(pv.q, i0);
+    const uint64_t qn = ((uint64_t)Q.nm1 << 32) | Q.nm0;
+    if (qn & low_mask64(K + 7)) return -1;
+    V3 rl, rh;
+    {
+        const int wd = P0 >> 5, sh = P0 & 31;
+        const Rec a = ld_rec(pv.r + wd), b = ld_rec(pv.r + wd + 1), c = ld_rec(pv.r + wd + 2), d = ld_rec(pv.r + wd + 3);
+        rl.a = funnel_r(a.x, b.x, sh); rl.b = funnel_r(b.x, c.x, sh); rl.c = funnel_r(c.x, d.x, sh);
+        rh.a = funnel_r(a.y, b.y, sh); rh.b = funnel_r(b.y, c.y, sh); rh.c = funnel_r(c.y, d.y, sh);
+        const uint32_t n0 = funnel_r(a.z, b.z, sh), n1 = funnel_r(b.z, c.z, sh), n2 = funnel_r(c.z, d.z, sh);
+        const int nr = K + P.mrd + 6;      // <= 96
+        if (n0 | (nr > 32 ? (n1 & low_mask32(nr - 32 > 32 ? 32 : nr - 32)) : 0u) | (nr > 64 ? (n2 & low_mask32(nr - 64)) : 0u)) return -1;
+    }
+    uint64_t ql = ((uint64_t)Q.lo1 << 32) | Q.lo0, qh = ((uint64_t)Q.hi1 << 32) | Q.hi0;
+    // valid reference positions of row k: x < k + mrd (mask grows by one bit per row)
+    const int n0 = P.mrd;
+    uint32_t m0 = low_mask32(n0 > 32 ? 32 : n0), m1 = n0 > 32 ? low_mask32(n0 - 32 > 32 ? 32 : n0 - 32) : 0u,
+             m2 = n0 > 64 ? low_mask32(n0 - 64) : 0u;
+    V3 mis_prev{0, 0, 0}, a2[4], a4[4];
+    for (int u = 0; u < 4; ++u) a2[u] = a4[u] = V3{0, 0, 0};
+    const int m_last = K + 6;
+    for (int mb = 0; mb <= m_last; mb += 4) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int u = 0; u < 4; ++u) {      // ring slots (m mod 4) are compile-time; body kept small (I-cache)
+            const int m = mb + u;
+            if (m > m_last) return 64;
+            // Mis_m: reference window against query base m
+            const uint32_t bl = 0u - ((uint32_t)(ql >> u) & 1u), bh = 0u - ((uint32_t)(qh >> u) & 1u);
+            V3 mis;
+            mis.a = (rl.a ^ bl) | (rh.a ^ bh);
+            mis.b = (rl.b ^ bl) | (rh.b ^ bh);
+            mis.c = (rl.c ^ bl) | (rh.c ^ bh);
+            // pairs: A2_{m-1}; fours: A4_{m-3}; sevens: S_{m-6}
+            const V3 p2 = v3_or_shr(mis_prev, mis, 1);              // A2_{m-1}
+            const V3 p4 = v3_or_shr(a2[(u + 1) % 4], p2, 2);        // A4_{m-3} = A2_{m-3} | A2_{m-1}>>2
+            const V3 s7 = v3_or_shr(a4[(u + 2) % 4], p4, 3);        // S_{m-6}  = A4_{m-6} | A4_{m-3}>>3
+            a2[(u + 3) % 4] = p2;                                   // slot (m-1) mod 4
+            a4[(u + 1) % 4] = p4;                                   // slot (m-3) mod 4
+            mis_prev = mis;
+            if (m >= 6) {
+                if ((~s7.a & m0) | (~s7.b & m1) | (~s7.c & m2)) return m - 6;
+                m2 = (m2 << 1) | (m1 >> 31);
+                m1 = (m1 << 1) | (m0 >> 31);
+                m0 = (m0 << 1) | 1u;
+            }
+        }
+        ql >>= 4;
+        qh >>= 4;
+    }
+    return 64;
+}
+
+// ------------------------------------------------------------------------------------------
 // One anchor hit, evaluated by ONE lane ahead of the sequential walk.  The result depends only
 // on the query position p (not on the parse state): the longest reference occurrence of the
 // mal-mer at p (ties -> smallest position, parser.cpp:516-530), and -- should the walk take it
@@ -485,22 +568,31 @@ LZ_HD void eval_hit(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uin
     if (!best_len) return;
     o_pos = (uint32_t)best_pos;
     uint32_t w2 = HIT_LIVE | (uint32_t)best_len, w3 = 0;
-    {   // forward
+    // both approximate extensions through ONE copy of extend_in_word (code size: I-cache)
+    uint32_t mw[2];
+    int lim[2];
+    {
         const int qn = p + best_len, pn = best_pos + best_len;
-        int lim = pv.Dq - qn;
-        if (pv.Dr - pn < lim) lim = pv.Dr - pn;
-        const uint32_t mw = lim > 0 ? mism32(pv.q, pv.Dq, qn, pv.r, pv.Dr, pn) : 0xFFFFFFFFu;
-        const ExtWord e = extend_in_word(mw, lim > 32 ? 32 : lim, lim > 32, P);
-        if (e.complete) w2 |= HIT_FWD | ((uint32_t)e.len << 6) | ((uint32_t)e.matches << 12);
-    }
-    {   // backward
-        const int lim = p < best_pos ? p : best_pos;
+        lim[0] = pv.Dq - qn;
+        if (pv.Dr - pn < lim[0]) lim[0] = pv.Dr - pn;
+        mw[0] = lim[0] > 0 ? mism32(pv.q, pv.Dq, qn, pv.r, pv.Dr, pn) : 0xFFFFFFFFu;
+        lim[1] = p < best_pos ? p : best_pos;
         BwdStream bs{&pv, p, best_pos};
-        const uint32_t mw = lim > 0 ? bs.word(0) : 0xFFFFFFFFu;
-        const ExtWord e = extend_in_word(mw, lim > 32 ? 32 : lim, lim > 32, P);
+        mw[1] = lim[1] > 0 ? bs.word(0) : 0xFFFFFFFFu;
+    }
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int dir = 0; dir < 2; ++dir) {
+        const uint32_t m = dir ? mw[1] : mw[0];
+        const int l = dir ? lim[1] : lim[0];
+        const ExtWord e = extend_in_word(m, l > 32 ? 32 : l, l > 32, P);
         if (e.complete) {
-            w2 |= HIT_BWD;
-            w3 = (uint32_t)e.len | ((uint32_t)e.matches << 6) | ((uint32_t)e.examined << 12);
+            if (dir == 0) w2 |= HIT_FWD | ((uint32_t)e.len << 6) | ((uint32_t)e.matches << 12);
+            else {
+                w2 |= HIT_BWD;
+                w3 = (uint32_t)e.len | ((uint32_t)e.matches << 6) | ((uint32_t)e.examined << 12);
+            }
         }
     }
     o_w2 = w2; o_w3 = w3;
@@ -572,6 +664,23 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int 
     s.pred = pn + fwd;
     s.lit = 0;
     s.re = s.i;
+}
+
+// query positions of the chunk at which some diagonal of [d_lo, d_hi) starts a run of >= msl equal
+// bases (bit k <-> i0+k).  Lanes own diagonals.
+template <class W, class PT>
+LZ_COLD uint64_t diag_seed_starts(W& w, const PairView& pv, const PT& P, const Planes64& Q, int i0, int P0, int d_lo, int d_hi)
+{
+    typename W::template Lanes<uint64_t> sm;
+    LZ_EACH(w, ln) sm[ln] = 0;
+    for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
+        LZ_EACH(w, ln)
+        {
+            const int d = dbase + ln;
+            if (d < d_hi) sm[ln] |= run_starts(diag_equal64(pv, Q, i0, P0, d), P.msl);
+        }
+    }
+    return w.or_u64(sm);
 }
 
 // best seed at chunk position k (parser.cpp:548-580): longest; ties -> closest to the
@@ -654,6 +763,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
     const int n_loop = Dq - P.msl;     // loop runs while i < n_loop (i + msl < Dq, :501)
     const int NC = 65 - P.msl;         // chunk size: msl-runs starting in the chunk fit 64 bits
 
+    int spec_i0 = -1, spec_K1 = 0, spec_ks = 64;   // speculative seed record of the match just taken
     int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
     typename W::template Lanes<uint32_t> hm, r_pos, r_w2, r_w3;
@@ -671,23 +781,30 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
                 // ---- new window: lane l probes positions win_base + 32 l + [0, 32)
                 win_base = i0 & ~31;
                 win_end = win_base + 1024 < n_loop ? win_base + 1024 : n_loop;
-                const uint32_t kmask = low_mask32(P.mal);
                 LZ_EACH(w, ln)
                 {
                     const int pos0 = win_base + 32 * ln;
                     uint32_t m = 0;
                     if (pos0 < win_end) {
                         const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
-#if defined(__CUDA_ARCH__)
-#pragma unroll 8
-#endif
-                        for (int t = 0; t < 32; ++t) {
-                            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t), nm = funnel_r(a.z, b.z, t);
-                            const bool ok = !(nm & kmask);
-                            const uint32_t bi = ok ? bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits) : 0u;
-                            const uint32_t bit = (ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u)) & (ok ? 1u : 0u);
-                            m |= bit << t;
+                        // positions whose mal-mer covers an N (rare: one test per 32 positions)
+                        uint32_t bad = 0;
+                        if (a.z | b.z) {
+                            const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
+                            uint64_t u = nz;
+                            for (int j = 1; j < P.mal; ++j) u |= nz >> j;
+                            bad = (uint32_t)u;
                         }
+#if defined(__CUDA_ARCH__)
+#pragma unroll 4
+#endif
+                        for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
+                            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+                            const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
+                            const uint32_t bw = ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u);
+                            m = (m >> 1) | (bw << 31);      // bit of position t ends up at bit t
+                        }
+                        m &= ~bad;
                         const int nv = win_end - pos0;
                         if (nv < 32) m &= low_mask32(nv);
                     }
@@ -719,6 +836,9 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             }
             w.sync();
             const int b_cnt = total < 32 ? total : 32;
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+            lz_batches++; lz_hits += b_cnt;
+#endif
             LZ_EACH(w, ln) r_p[ln] = ln < b_cnt ? win_base + (int)list[ln] : 0x7FFFFFFF;
             w.sync();
             b_cover = total <= 32 ? win_end : w.get(r_p, 31) + 1;
@@ -726,6 +846,19 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             {
                 uint32_t a = 0, b = 0, c = 0;
                 if (ln < b_cnt) eval_hit(pv, P, r_p[ln], a, b, c);
+                if (PT::kSpecSeeds && (b & HIT_FWD) && P.mqd <= SPEC_MAX_K) {
+                    // the prediction window this hit opens if it is taken (see spec_first_seed):
+                    // scanned up to the next hit of the batch (inclusive) or the end of what the
+                    // batch covers
+                    const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
+                    const int si0 = r_p[ln] + adv, sP0 = (int)a + adv;
+                    int idx = ln + 1;
+                    while (idx < b_cnt && win_base + (int)list[idx] < si0) ++idx;
+                    int K = idx < b_cnt ? win_base + (int)list[idx] - si0 : b_cover - 1 - si0;
+                    if (K > P.mqd) K = P.mqd;
+                    const int ks = spec_first_seed(pv, P, si0, sP0, K);
+                    if (ks >= 0) c |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
+                }
                 r_pos[ln] = a; r_w2[ln] = b; r_w3[ln] = c;
             }
         }
@@ -764,6 +897,12 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         int n = P.mqd + 1 - lit0;
         if (n > NC) n = NC;
         if (n > b_cover - i0) n = b_cover - i0;
+        // seeds of this step already known?  (record of the anchor match that ended at i0)
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+        lz_pred_steps++;
+#endif
+        const bool use_spec = PT::kSpecSeeds && lit0 == 0 && i0 == spec_i0 && spec_K1 > 0;
+        if (use_spec && n > spec_K1) n = spec_K1;
         // the first anchor record inside the chunk that counts here (position 0 == "none", :604)
         typename W::template Lanes<int> c;
         LZ_EACH(w, ln)
@@ -776,16 +915,21 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         // seeds: runs of >= msl equal bases along the diagonals [d_lo, d_hi) of the window
         const Planes64 Q = ext64(pv.q, i0);
         const int d_lo = -(ns - 1), d_hi = lit0 + P.mrd;
-        typename W::template Lanes<uint64_t> sm;
-        LZ_EACH(w, ln) sm[ln] = 0;
-        for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
-            LZ_EACH(w, ln)
-            {
-                const int d = dbase + ln;
-                if (d < d_hi) sm[ln] |= run_starts(diag_equal64(pv, Q, i0, P0, d), P.msl);
-            }
+        uint64_t cand;
+        if (use_spec) cand = spec_ks < ns ? 1ull << spec_ks : 0ull;   // only the first seed matters
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+        if (use_spec) {   // TEST ONLY (tests/emul): the record must agree with the diagonal scan
+            uint64_t chk = 0;
+            for (int d = d_lo; d < d_hi; ++d) chk |= run_starts(diag_equal64(pv, Q, i0, P0, d), P.msl);
+            chk &= low_mask64(ns);
+            const uint64_t first = chk ? chk & (0 - chk) : 0;
+            if (first != cand) { lz_spec_mismatches++; cand = first; }
+            lz_spec_used++;
         }
-        uint64_t cand = w.or_u64(sm) & low_mask64(ns);
+#endif
+        if (!use_spec) {
+            cand = diag_seed_starts(w, pv, P, Q, i0, P0, d_lo, d_hi) & low_mask64(ns);
+        }
 
         for (;;) {
             const int ks = cand ? ctz64(cand) : 64;
@@ -834,7 +978,18 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             s.pred = s.lit > P.mqd ? -1 : s.pred + ns;
         }
         }
-        if (matched) take_match(w, pv, P, s, m_qi, m_lit, m_pred, m_pos, m_len, m_w2, m_w3);
+        if (matched) {
+            take_match(w, pv, P, s, m_qi, m_lit, m_pred, m_pos, m_len, m_w2, m_w3);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+            lz_matches++;
+#endif
+            spec_K1 = 0;
+            if (PT::kSpecSeeds && (m_w2 & HIT_FWD)) {    // s.i / s.pred came from the record
+                spec_i0 = s.i;
+                spec_K1 = (int)((m_w3 >> 18) & 63u);
+                spec_ks = (int)((m_w3 >> 24) & 127u);
+            }
+        }
     }
 
     // tail (:710-713): with a live prediction the rest is compared against the reference shifted

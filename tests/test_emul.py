@@ -40,3 +40,18 @@ def test_kernel_source_vs_oracle_on_fresh_inputs(emul, seed, params):
     names, seqs = synth.families(2, 4, 1500, 4000, seed=seed, block=(100, 400))
     ss = hostio.SeqSet(names, seqs)
     assert np.array_equal(emul.run_rows(ss, params), Oracle().run_rows(ss, params))
+
+
+def test_speculative_seed_records_agree_with_diagonal_scan(emul):
+    """The emulation is built with LZ_SPEC_CHECK: every prediction step that uses a per-hit
+    speculative seed record (spec_first_seed) also runs the warp-cooperative diagonal scan and
+    counts disagreements.  Single-threaded run so the plain counters are exact."""
+    import ctypes as C
+    ss = mg.get_set("example")
+    emul.run_rows(ss, None, threads=1)
+    names, seqs = synth.families(2, 3, 3000, 5000, seed=77, d_lo=0.02, d_hi=0.35)
+    emul.run_rows(hostio.SeqSet(names, seqs), None, threads=1)
+    used, bad = C.c_long(), C.c_long()
+    emul.lib.lzani_emul_spec_stats(C.byref(used), C.byref(bad))
+    assert used.value > 1000, "speculative records were not exercised"
+    assert bad.value == 0
