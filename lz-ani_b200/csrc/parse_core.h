@@ -413,7 +413,8 @@ LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const PT& P)
     {
         // the window can only overflow at a mismatch, and not before the (am+1)-th one
         uint32_t t = m;
-        for (int c = 0; c < P.am && t; ++c) t &= t - 1u;
+        const int na = P.am < 32 ? P.am : 32;
+        for (int c = 0; c < na; ++c) t &= t - 1u;       // no early exit: lanes stay together
         const uint64_t x = (uint64_t)m << 32;          // positions before the stream: matches
         const uint64_t wmask = low_mask64(P.aw);
         while (t) {
@@ -457,6 +458,8 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
     return r;
 }
 constexpr int SPEC_MAX_K = 57;
+constexpr int LZ_WIN_WORDS = 4;                    // hit-mask words per lane and window
+constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
 static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0;   // TEST ONLY counters (tests/emul)
 #endif
@@ -536,39 +539,47 @@ constexpr uint32_t HIT_FWD = 1u << 20;     // fwd fields valid
 constexpr uint32_t HIT_BWD = 1u << 21;     // bwd fields valid
 constexpr int HIT_MAX_CHAIN = 6;           // matching-tag slots one lane inspects before deferring
 
+// Stage A: table probe + first-word comparison.  Single-exit loop so that the lanes of a batch
+// reconverge behind it (the caller also puts a warp sync between the stages).
 template <class PT>
-LZ_HD void eval_hit(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uint32_t& o_w2, uint32_t& o_w3)
+LZ_HD void hit_probe(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uint32_t& o_w2)
 {
-    o_pos = 0; o_w2 = 0; o_w3 = 0;
+    o_pos = 0; o_w2 = 0;
     uint32_t lo, hi, nm;
     ext3(pv.q, p, lo, hi, nm);
-    if (nm & low_mask32(P.mal)) return;
     const uint64_t key = kmer_key(lo, hi, P.mal);
     const uint32_t tmask = (1u << pv.tbits) - 1u;
     const uint32_t tag = table_tag(key, P.mal);
     uint32_t h = table_home(key, pv.tbits);
     int best_len = 0, best_pos = 0, seen = 0;
     bool defer = false;
-    for (;;) {
+    bool go = !(nm & low_mask32(P.mal));
+    while (go) {
         const uint64_t slot = ld_u64(pv.table + (h & tmask));
-        if (slot == LZ_EMPTY) break;
-        if ((uint32_t)(slot >> 32) == tag) {
-            if (++seen > HIT_MAX_CHAIN) { defer = true; break; }
+        ++h;
+        if (slot == LZ_EMPTY) go = false;
+        else if ((uint32_t)(slot >> 32) == tag) {
             const int rp = (int)(uint32_t)slot;
             uint32_t rl, rh, rn;
             ext3(pv.r, rp, rl, rh, rn);
             const uint32_t m0 = (lo ^ rl) | (hi ^ rh) | nm | rn;
-            if (!m0) { defer = true; break; }            // >= 32 equal bases
-            const int len = ctz32(m0);
-            if (len >= P.mal && (len > best_len || (len == best_len && rp < best_pos))) { best_len = len; best_pos = rp; }
+            if (++seen > HIT_MAX_CHAIN || !m0) { defer = true; go = false; }   // long chain / >= 32 equal bases
+            else {
+                const int len = ctz32(m0);
+                if (len >= P.mal && (len > best_len || (len == best_len && rp < best_pos))) { best_len = len; best_pos = rp; }
+            }
         }
-        ++h;
     }
-    if (defer) { o_w2 = HIT_LIVE | HIT_DEFER; return; }
-    if (!best_len) return;
-    o_pos = (uint32_t)best_pos;
-    uint32_t w2 = HIT_LIVE | (uint32_t)best_len, w3 = 0;
-    // both approximate extensions through ONE copy of extend_in_word (code size: I-cache)
+    if (defer) o_w2 = HIT_LIVE | HIT_DEFER;
+    else if (best_len) { o_pos = (uint32_t)best_pos; o_w2 = HIT_LIVE | (uint32_t)best_len; }
+}
+
+// Stage B: both approximate extensions of a probed hit, inside one stream word each
+template <class PT>
+LZ_HD void hit_extend(const PairView& pv, const PT& P, int p, int best_pos, uint32_t& w2, uint32_t& w3)
+{
+    const int best_len = (int)(w2 & 63u);
+    // both directions through ONE copy of extend_in_word (code size: I-cache)
     uint32_t mw[2];
     int lim[2];
     {
@@ -580,6 +591,7 @@ LZ_HD void eval_hit(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uin
         BwdStream bs{&pv, p, best_pos};
         mw[1] = lim[1] > 0 ? bs.word(0) : 0xFFFFFFFFu;
     }
+    w3 = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
 #endif
@@ -595,7 +607,6 @@ LZ_HD void eval_hit(const PairView& pv, const PT& P, int p, uint32_t& o_pos, uin
             }
         }
     }
-    o_w2 = w2; o_w3 = w3;
 }
 
 struct ParseState {
@@ -606,7 +617,7 @@ struct ParseState {
 };
 
 // One match found at query position qi (parser.cpp:626-698), counts only.  (w2, w3) is the
-// speculative record of eval_hit() when the match IS that anchor, else w2 == 0.
+// speculative record of hit_probe()/hit_extend() when the match IS that anchor, else w2 == 0.
 template <class W, class PT>
 LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int qi, int lit_k, int pred_k,
                       int best_pos, int best_len, uint32_t w2, uint32_t w3)
@@ -744,7 +755,7 @@ LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q,
 //   window (<= 1024 query positions): every lane probes the anchor presence bitmap for its own
 //          32 consecutive positions -> hit masks, one word per lane;
 //   batch  (<= 32 hits of the window, in position order): lane j evaluates hit j on its own
-//          (eval_hit) -- table probe, match length, both approximate extensions -- ahead of
+//          (hit_probe, hit_extend, spec_first_seed) -- table probe, match length, both approximate extensions -- ahead of
 //          the walk; this is where the lanes do independent work;
 //   walk   : the sequential state machine of parser.cpp:501-708 over chunks of <= 65-msl
 //          positions, consuming the batch records in order.  Without a prediction it jumps
@@ -766,9 +777,13 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
     int spec_i0 = -1, spec_K1 = 0, spec_ks = 64;   // speculative seed record of the match just taken
     int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
-    typename W::template Lanes<uint32_t> hm, r_pos, r_w2, r_w3;
+    typename W::template Lanes<uint32_t> hm[LZ_WIN_WORDS], r_pos, r_w2, r_w3;
     typename W::template Lanes<int> r_p;
-    LZ_EACH(w, ln) { hm[ln] = 0; r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; }
+    LZ_EACH(w, ln)
+    {
+        for (int q = 0; q < LZ_WIN_WORDS; ++q) hm[q][ln] = 0;
+        r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF;
+    }
 
     while (s.i < n_loop) {
         const int i0 = s.i;
@@ -778,60 +793,70 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         uint32_t m_w2 = 0, m_w3 = 0;
         if (i0 >= b_cover) {
             if (i0 >= win_end) {
-                // ---- new window: lane l probes positions win_base + 32 l + [0, 32)
+                // ---- new window: lane l probes positions win_base + LZ_WIN_LANE*l + [0, LZ_WIN_LANE)
+                // (large enough that batches of 32 hits are normally full: ~2.4 % of the positions of
+                // an unrelated pair hit the bitmap)
                 win_base = i0 & ~31;
-                win_end = win_base + 1024 < n_loop ? win_base + 1024 : n_loop;
-                LZ_EACH(w, ln)
-                {
-                    const int pos0 = win_base + 32 * ln;
-                    uint32_t m = 0;
-                    if (pos0 < win_end) {
-                        const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
-                        // positions whose mal-mer covers an N (rare: one test per 32 positions)
-                        uint32_t bad = 0;
-                        if (a.z | b.z) {
-                            const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
-                            uint64_t u = nz;
-                            for (int j = 1; j < P.mal; ++j) u |= nz >> j;
-                            bad = (uint32_t)u;
-                        }
+                win_end = win_base + 32 * LZ_WIN_LANE < n_loop ? win_base + 32 * LZ_WIN_LANE : n_loop;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+                for (int q = 0; q < LZ_WIN_WORDS; ++q) {
+                    LZ_EACH(w, ln)
+                    {
+                        const int pos0 = win_base + LZ_WIN_LANE * ln + 32 * q;
+                        uint32_t m = 0;
+                        if (pos0 < win_end) {
+                            const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
+                            // positions whose mal-mer covers an N (rare: one test per 32 positions)
+                            uint32_t bad = 0;
+                            if (a.z | b.z) {
+                                const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
+                                uint64_t u = nz;
+                                for (int j = 1; j < P.mal; ++j) u |= nz >> j;
+                                bad = (uint32_t)u;
+                            }
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
-                        for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
-                            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
-                            const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
-                            const uint32_t bw = ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u);
-                            m = (m >> 1) | (bw << 31);      // bit of position t ends up at bit t
+                            for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
+                                const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+                                const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
+                                const uint32_t bw = ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u);
+                                m = (m >> 1) | (bw << 31);      // bit of position t ends up at bit t
+                            }
+                            m &= ~bad;
+                            const int nv = win_end - pos0;
+                            if (nv < 32) m &= low_mask32(nv);
                         }
-                        m &= ~bad;
-                        const int nv = win_end - pos0;
-                        if (nv < 32) m &= low_mask32(nv);
+                        hm[q][ln] = m;
                     }
-                    hm[ln] = m;
                 }
             }
             // ---- new batch: the first <= 32 hits at or after i0
-            typename W::template Lanes<uint32_t> mm;
             typename W::template Lanes<int> cnt, pre;
             LZ_EACH(w, ln)
             {
-                const int rel = i0 - (win_base + 32 * ln);
-                uint32_t m = hm[ln];
-                if (rel >= 32) m = 0;
-                else if (rel > 0) m &= ~low_mask32(rel);
-                mm[ln] = m;
-                cnt[ln] = popc32(m);
+                int c = 0;
+                for (int q = 0; q < LZ_WIN_WORDS; ++q) {
+                    const int rel = i0 - (win_base + LZ_WIN_LANE * ln + 32 * q);
+                    if (rel >= 32) hm[q][ln] = 0;                        // behind the walk: never needed again
+                    else if (rel > 0) hm[q][ln] &= ~low_mask32(rel);
+                    c += popc32(hm[q][ln]);
+                }
+                cnt[ln] = c;
             }
             w.exscan_add(pre, cnt);
             const int total = w.add_i32(cnt);
             LZ_EACH(w, ln)
             {
-                uint32_t m = mm[ln];
                 int idx = pre[ln];
-                while (m && idx < 32) {
-                    list[idx++] = (uint16_t)(32 * ln + ctz32(m));
-                    m &= m - 1u;
+                for (int q = 0; q < LZ_WIN_WORDS && idx < 32; ++q) {
+                    uint32_t m = hm[q][ln];
+                    while (m && idx < 32) {
+                        list[idx++] = (uint16_t)(LZ_WIN_LANE * ln + 32 * q + ctz32(m));
+                        m &= m - 1u;
+                    }
                 }
             }
             w.sync();
@@ -842,24 +867,39 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             LZ_EACH(w, ln) r_p[ln] = ln < b_cnt ? win_base + (int)list[ln] : 0x7FFFFFFF;
             w.sync();
             b_cover = total <= 32 ? win_end : w.get(r_p, 31) + 1;
+            // three stages, each entered by the whole warp (sync = reconvergence point): lanes take
+            // different numbers of probe / scan iterations and must not stay split afterwards
             LZ_EACH(w, ln)
             {
-                uint32_t a = 0, b = 0, c = 0;
-                if (ln < b_cnt) eval_hit(pv, P, r_p[ln], a, b, c);
-                if (PT::kSpecSeeds && (b & HIT_FWD) && P.mqd <= SPEC_MAX_K) {
-                    // the prediction window this hit opens if it is taken (see spec_first_seed):
-                    // scanned up to the next hit of the batch (inclusive) or the end of what the
-                    // batch covers
-                    const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
-                    const int si0 = r_p[ln] + adv, sP0 = (int)a + adv;
-                    int idx = ln + 1;
-                    while (idx < b_cnt && win_base + (int)list[idx] < si0) ++idx;
-                    int K = idx < b_cnt ? win_base + (int)list[idx] - si0 : b_cover - 1 - si0;
-                    if (K > P.mqd) K = P.mqd;
-                    const int ks = spec_first_seed(pv, P, si0, sP0, K);
-                    if (ks >= 0) c |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
+                uint32_t a = 0, b = 0;
+                if (ln < b_cnt) hit_probe(pv, P, r_p[ln], a, b);
+                r_pos[ln] = a; r_w2[ln] = b; r_w3[ln] = 0;
+            }
+            w.sync();
+            LZ_EACH(w, ln)
+            {
+                if ((r_w2[ln] & (HIT_LIVE | HIT_DEFER)) == HIT_LIVE) hit_extend(pv, P, r_p[ln], (int)r_pos[ln], r_w2[ln], r_w3[ln]);
+            }
+            w.sync();
+            if (PT::kSpecSeeds && P.mqd <= SPEC_MAX_K) {
+                LZ_EACH(w, ln)
+                {
+                    if (r_w2[ln] & HIT_FWD) {
+                        // the prediction window this hit opens if it is taken (see spec_first_seed):
+                        // scanned up to the next hit of the batch (inclusive) or the end of what the
+                        // batch covers
+                        const uint32_t b = r_w2[ln];
+                        const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
+                        const int si0 = r_p[ln] + adv, sP0 = (int)r_pos[ln] + adv;
+                        int idx = ln + 1;
+                        while (idx < b_cnt && win_base + (int)list[idx] < si0) ++idx;
+                        int K = idx < b_cnt ? win_base + (int)list[idx] - si0 : b_cover - 1 - si0;
+                        if (K > P.mqd) K = P.mqd;
+                        const int ks = spec_first_seed(pv, P, si0, sP0, K);
+                        if (ks >= 0) r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
+                    }
                 }
-                r_pos[ln] = a; r_w2[ln] = b; r_w3[ln] = c;
+                w.sync();
             }
         }
 
@@ -913,20 +953,22 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         const int ns = ja >= 0 ? ka + 1 : n;          // positions examined by this step
 
         // seeds: runs of >= msl equal bases along the diagonals [d_lo, d_hi) of the window
-        const Planes64 Q = ext64(pv.q, i0);
+        Planes64 Q{};                    // loaded only when a seed has to be looked at
         const int d_lo = -(ns - 1), d_hi = lit0 + P.mrd;
         uint64_t cand;
         if (use_spec) cand = spec_ks < ns ? 1ull << spec_ks : 0ull;   // only the first seed matters
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
         if (use_spec) {   // TEST ONLY (tests/emul): the record must agree with the diagonal scan
             uint64_t chk = 0;
-            for (int d = d_lo; d < d_hi; ++d) chk |= run_starts(diag_equal64(pv, Q, i0, P0, d), P.msl);
+            const Planes64 Qc = ext64(pv.q, i0);
+            for (int d = d_lo; d < d_hi; ++d) chk |= run_starts(diag_equal64(pv, Qc, i0, P0, d), P.msl);
             chk &= low_mask64(ns);
             const uint64_t first = chk ? chk & (0 - chk) : 0;
             if (first != cand) { lz_spec_mismatches++; cand = first; }
             lz_spec_used++;
         }
 #endif
+        if (!use_spec || cand) Q = ext64(pv.q, i0);
         if (!use_spec) {
             cand = diag_seed_starts(w, pv, P, Q, i0, P0, d_lo, d_hi) & low_mask64(ns);
         }
