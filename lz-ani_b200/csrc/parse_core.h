@@ -461,7 +461,7 @@ constexpr int SPEC_MAX_K = 57;
 constexpr int LZ_WIN_WORDS = 4;                    // hit-mask words per lane and window
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
-static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0;   // TEST ONLY counters (tests/emul)
+static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0;   // TEST ONLY counters (tests/emul)
 #endif
 template <class PT>
 LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
@@ -900,6 +900,61 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
                     }
                 }
                 w.sync();
+            }
+        }
+
+        // ---- FAST PATH.  The walk stands right behind an anchor match taken from its record
+        // (prediction on, no literals yet, seeds of the window known from the speculative scan) and
+        // the next thing that happens is one of the two plain events of an unrelated pair:
+        //   * the next anchor record lies inside the window, no seed before or at it, and it is far
+        //     from the prediction (> mrd): a distant match taken entirely from its record;
+        //   * nothing at all for mqd+1 positions: the prediction expires.
+        // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
+        // general code below, which re-derives the same step.
+        if (PT::kSpecSeeds && s.pred >= 0 && s.lit == 0 && i0 == spec_i0 && spec_K1 > 0) {
+            typename W::template Lanes<int> c;
+            LZ_EACH(w, ln) c[ln] = r_p[ln] >= i0 && (r_w2[ln] & HIT_LIVE);
+            const uint32_t vm = w.ballot(c);
+            const int j = vm ? ctz32(vm) : 0;
+            const int qi = vm ? w.get(r_p, j) : 0x7FFFFFFF;
+            const int ka = qi - i0;
+            if (ka < spec_K1 && ka <= P.mqd) {
+                const uint32_t w2 = w.get(r_w2, j);
+                const int a_pos = (int)w.get(r_pos, j);
+                int dist = a_pos - (s.pred + ka);
+                if (dist < 0) dist = -dist;
+                if (spec_ks > ka && (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD && a_pos != 0 && dist > P.mrd) {
+                    const uint32_t w3 = w.get(r_w3, j);
+                    const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
+                    const int kept_end = keep ? s.re : s.kept_end;
+                    const int run = qi - kept_end;
+                    int lim = run < qi ? run : qi;
+                    if (a_pos < lim) lim = a_pos;
+                    if (run <= 0 || ((w2 & HIT_BWD) && lim >= (int)((w3 >> 12) & 63u))) {
+                        if (keep) { s.totM += s.curM; s.totX += s.curX; ++s.totN; s.kept_end = kept_end; }
+                        const int back = run > 0 ? (int)(w3 & 63u) : 0, bm = run > 0 ? (int)((w3 >> 6) & 63u) : 0;
+                        const int len = (int)(w2 & 63u), fwd = (int)((w2 >> 6) & 63u), fm = (int)((w2 >> 12) & 63u);
+                        s.curM = bm + len + fm;
+                        s.curX = back - bm + fwd - fm;
+                        s.rs = qi - back;
+                        s.i = qi + len + fwd;
+                        s.pred = a_pos + len + fwd;
+                        s.re = s.i;
+                        spec_i0 = s.i;
+                        spec_K1 = (int)((w3 >> 18) & 63u);
+                        spec_ks = (int)((w3 >> 24) & 127u);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                        lz_matches++; lz_fast++;
+#endif
+                        continue;
+                    }
+                }
+            } else if (spec_K1 > P.mqd && spec_ks >= 64 && ka > P.mqd) {
+                // mqd+1 literal steps, then the prediction is dropped (:699-707)
+                s.i = i0 + P.mqd + 1;
+                s.lit = P.mqd + 1;
+                s.pred = -1;
+                continue;
             }
         }
 

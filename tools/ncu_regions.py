@@ -16,16 +16,21 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MARKS = [("equal_len_coop", "int equal_len_coop("), ("approx_extend", "void approx_extend("),
          ("both_ways", "int both_ways_best("), ("anchor_lookup", "void anchor_lookup("),
          ("diag_helpers", "struct DiagWord"), ("extend_in_word", "struct ExtWord"), ("spec_first_seed", "struct V3"),
-         ("eval_hit", "void eval_hit("), ("take_match", "void take_match("), ("diag_seed_starts", "uint64_t diag_seed_starts("),
+         ("hit_probe", "void hit_probe("), ("hit_extend", "void hit_extend("), ("take_match", "void take_match("), ("diag_seed_starts", "uint64_t diag_seed_starts("),
          ("best_seed", "void best_seed("), ("pp:init", "PairResult parse_pair("), ("pp:window_scan", "// ---- new window"),
-         ("pp:batch_list", "// ---- new batch"), ("pp:batch_eval", "b_cover = total <= 32"), ("pp:nopred", "// ---- no prediction"),
+         ("pp:batch_list", "// ---- new batch"), ("pp:batch_eval", "b_cover = total <= 32"), ("pp:batch_spec", "if (PT::kSpecSeeds && P.mqd <= SPEC_MAX_K)"), ("pp:nopred", "// ---- no prediction"),
          ("pp:pred", "// ---- prediction mode"), ("pp:take", "if (matched) {"), ("pp:tail", "// tail (:710-713)")]
 
 
 def main():
     src_csv, sass, func, pairs = sys.argv[1], sys.argv[2], sys.argv[3], float(sys.argv[4])
     src = open(os.path.join(ROOT, "lz-ani_b200", "csrc", "parse_core.h")).read().split("\n")
-    starts = sorted((next(i for i, x in enumerate(src) if pat in x) + 1, nm) for nm, pat in MARKS)
+    starts = []
+    for nm, pat in MARKS:
+        hit = [i for i, x in enumerate(src) if pat in x]
+        if hit:
+            starts.append((hit[0] + 1, nm))
+    starts.sort()
 
     def region(line):
         r = "head"
