@@ -911,50 +911,58 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         //   * nothing at all for mqd+1 positions: the prediction expires.
         // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
         // general code below, which re-derives the same step.
-        if (PT::kSpecSeeds && s.pred >= 0 && s.lit == 0 && i0 == spec_i0 && spec_K1 > 0) {
+        if (PT::kSpecSeeds && (s.pred < 0 || (s.lit == 0 && i0 == spec_i0 && spec_K1 > 0))) {
             typename W::template Lanes<int> c;
             LZ_EACH(w, ln) c[ln] = r_p[ln] >= i0 && (r_w2[ln] & HIT_LIVE);
             const uint32_t vm = w.ballot(c);
             const int j = vm ? ctz32(vm) : 0;
             const int qi = vm ? w.get(r_p, j) : 0x7FFFFFFF;
             const int ka = qi - i0;
-            if (ka < spec_K1 && ka <= P.mqd) {
-                const uint32_t w2 = w.get(r_w2, j);
-                const int a_pos = (int)w.get(r_pos, j);
-                int dist = a_pos - (s.pred + ka);
-                if (dist < 0) dist = -dist;
-                if (spec_ks > ka && (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD && a_pos != 0 && dist > P.mrd) {
-                    const uint32_t w3 = w.get(r_w3, j);
-                    const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
-                    const int kept_end = keep ? s.re : s.kept_end;
-                    const int run = qi - kept_end;
-                    int lim = run < qi ? run : qi;
-                    if (a_pos < lim) lim = a_pos;
-                    if (run <= 0 || ((w2 & HIT_BWD) && lim >= (int)((w3 >> 12) & 63u))) {
-                        if (keep) { s.totM += s.curM; s.totX += s.curX; ++s.totN; s.kept_end = kept_end; }
-                        const int back = run > 0 ? (int)(w3 & 63u) : 0, bm = run > 0 ? (int)((w3 >> 6) & 63u) : 0;
-                        const int len = (int)(w2 & 63u), fwd = (int)((w2 >> 6) & 63u), fm = (int)((w2 >> 12) & 63u);
-                        s.curM = bm + len + fm;
-                        s.curX = back - bm + fwd - fm;
-                        s.rs = qi - back;
-                        s.i = qi + len + fwd;
-                        s.pred = a_pos + len + fwd;
-                        s.re = s.i;
-                        spec_i0 = s.i;
-                        spec_K1 = (int)((w3 >> 18) & 63u);
-                        spec_ks = (int)((w3 >> 24) & 127u);
-#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
-                        lz_matches++; lz_fast++;
-#endif
+            const uint32_t w2 = w.get(r_w2, j);
+            const int a_pos = (int)w.get(r_pos, j);
+            bool plain = vm && (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
+            if (s.pred >= 0) {
+                if (ka > P.mqd) {
+                    plain = false;
+                    if (spec_K1 > P.mqd && spec_ks >= 64) {
+                        // mqd+1 literal steps, then the prediction is dropped (:699-707)
+                        s.i = i0 + P.mqd + 1;
+                        s.lit = P.mqd + 1;
+                        s.pred = -1;
                         continue;
                     }
+                } else {
+                    int dist = a_pos - (s.pred + ka);
+                    if (dist < 0) dist = -dist;
+                    plain = plain && ka < spec_K1 && spec_ks > ka && a_pos != 0 && dist > P.mrd;
                 }
-            } else if (spec_K1 > P.mqd && spec_ks >= 64 && ka > P.mqd) {
-                // mqd+1 literal steps, then the prediction is dropped (:699-707)
-                s.i = i0 + P.mqd + 1;
-                s.lit = P.mqd + 1;
-                s.pred = -1;
-                continue;
+            }
+            if (plain) {
+                const uint32_t w3 = w.get(r_w3, j);
+                const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
+                const int kept_end = keep ? s.re : s.kept_end;
+                const int run = qi - kept_end;
+                int lim = run < qi ? run : qi;
+                if (a_pos < lim) lim = a_pos;
+                if (run <= 0 || ((w2 & HIT_BWD) && lim >= (int)((w3 >> 12) & 63u))) {
+                    if (keep) { s.totM += s.curM; s.totX += s.curX; ++s.totN; s.kept_end = kept_end; }
+                    const int back = run > 0 ? (int)(w3 & 63u) : 0, bm = run > 0 ? (int)((w3 >> 6) & 63u) : 0;
+                    const int len = (int)(w2 & 63u), fwd = (int)((w2 >> 6) & 63u), fm = (int)((w2 >> 12) & 63u);
+                    s.curM = bm + len + fm;
+                    s.curX = back - bm + fwd - fm;
+                    s.rs = qi - back;
+                    s.i = qi + len + fwd;
+                    s.pred = a_pos + len + fwd;
+                    s.lit = 0;
+                    s.re = s.i;
+                    spec_i0 = s.i;
+                    spec_K1 = (int)((w3 >> 18) & 63u);
+                    spec_ks = (int)((w3 >> 24) & 127u);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                    lz_matches++; lz_fast++;
+#endif
+                    continue;
+                }
             }
         }
 
