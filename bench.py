@@ -55,6 +55,20 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def measured_traffic(n_genomes: int, world: int):
+    """DRAM bytes per k_parse_pairs launch from the committed ncu capture of THIS workload
+    (profiles/traffic.json, written from `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`);
+    None when no capture matches the configuration."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        t = json.load(open(p))
+        if int(t["genomes"]) == n_genomes and world == 1:
+            return float(t["dram_bytes_per_launch"])
+    except Exception:
+        pass
+    return None
+
+
 def make_set(n_genomes: int):
     cache = f"/tmp/lzani_synth_{synth.SEED}_{n_genomes}.npz"
     if os.path.exists(cache):
@@ -273,7 +287,7 @@ def main():
     alg_bytes = BYTES_PER_QUERY_BASE * my_qbases + 12.0 * my_pairs
     achieved = alg_bytes / (parse_ms / args.steps / 1e3) / 1e9 if parse_ms > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": "k_parse_pairs", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": measured_traffic(n, world), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": parse_ms / args.steps,
                 "index_kernel_ms": index_ms / args.steps,
                 "index_algorithmic_bytes": BYTES_PER_REF_POS * r_bases}

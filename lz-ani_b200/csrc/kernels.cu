@@ -81,7 +81,7 @@ k_build_index(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 // batch's first pair) belongs to the batch row found in row_off; its query is q_ids[k] or, for
 // the dense all2all list, the (k - row_off[row])-th id different from the reference.
 template <class PT>
-__global__ void __launch_bounds__(LZ_PARSE_THREADS)
+__global__ void __launch_bounds__(LZ_PARSE_THREADS, LZ_PARSE_MIN_BLOCKS)
 k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
               const uint32_t* __restrict__ row_ref, const RefIndex* __restrict__ row_idx,
               const uint64_t* __restrict__ row_off, uint32_t n_rows, const uint32_t* __restrict__ q_ids,
@@ -90,8 +90,8 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
               int3* __restrict__ out)
 {
     DevWarp w((int)(threadIdx.x & 31u));
-    __shared__ uint16_t hit_list[LZ_PARSE_THREADS / 32][32];
-    uint16_t* list = hit_list[threadIdx.x >> 5];
+    __shared__ WarpScratch scratch[LZ_PARSE_THREADS / 32];
+    WarpScratch* sc = &scratch[threadIdx.x >> 5];
     for (;;) {
         unsigned long long k = 0;
         if (w.lane == 0) k = atomicAdd(counter, 1ull);
@@ -116,7 +116,7 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
         pv.bbits = ix.bbits;
         pv.table = table_pool + ix.table_slot;
         pv.tbits = ix.tbits;
-        const PairResult res = parse_pair(w, pv, P, list);
+        const PairResult res = parse_pair(w, pv, P, sc);
         if (w.lane == 0) out[k] = make_int3(res.m, res.x, res.n);
     }
 }

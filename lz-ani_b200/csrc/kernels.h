@@ -6,6 +6,9 @@
 #include "layout.h"
 
 #define LZ_PARSE_THREADS 128
+#ifndef LZ_PARSE_MIN_BLOCKS
+#define LZ_PARSE_MIN_BLOCKS 5
+#endif
 
 namespace lzani {
 

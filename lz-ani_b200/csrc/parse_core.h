@@ -153,6 +153,7 @@ LZ_COLD void approx_extend(W& w, const AnyStream& st, int limit, const PT& P, in
     uint32_t carry = 0;           // stream word preceding the chunk (0: "matches" before the start)
     int matches_before = 0;       // matches in stream positions below the chunk
     const uint64_t wmask = low_mask64(P.aw);
+    LZ_ROLLED
     for (int base = 0;; base += 1024) {
         typename W::template Lanes<uint32_t> cur, prev;
         LZ_EACH(w, ln)
@@ -241,6 +242,7 @@ LZ_COLD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_r
     w.exscan_add(pl, cl);
     w.exscan_add(pr, cr);
     int best = 0;
+    LZ_ROLLED
     for (int s0 = 0; s0 <= span; s0 += 32) {
         typename W::template Lanes<int> sl, sr;
         typename W::template Lanes<uint32_t> wl, wr;
@@ -460,6 +462,12 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
 constexpr int SPEC_MAX_K = 57;
 constexpr int LZ_WIN_WORDS = 4;                    // hit-mask words per lane and window
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
+// per-warp scratch (shared memory on the device): the hit masks of the current window, one column
+// per lane, and the hit list of the current batch
+struct WarpScratch {
+    uint32_t hm[LZ_WIN_WORDS][32];
+    uint16_t list[32];
+};
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
 static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0;   // TEST ONLY counters (tests/emul)
 #endif
@@ -684,6 +692,7 @@ LZ_COLD uint64_t diag_seed_starts(W& w, const PairView& pv, const PT& P, const P
 {
     typename W::template Lanes<uint64_t> sm;
     LZ_EACH(w, ln) sm[ln] = 0;
+    LZ_ROLLED
     for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
         LZ_EACH(w, ln)
         {
@@ -703,6 +712,7 @@ LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q,
     int sl = 0;
     uint32_t skey = 0xFFFFFFFFu;
     const int qi = i0 + k;
+    LZ_ROLLED
     for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
         typename W::template Lanes<int> len, more;
         typename W::template Lanes<uint32_t> dk;
@@ -749,6 +759,49 @@ LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q,
     }
 }
 
+// ---- the next anchor event at or after query position i0 (and below `lim`).
+// Consecutive hit positions are almost always one longer match seen twice, and the second is then
+// skipped by the walk.  So only the first position of a run of consecutive hits (a run never crosses
+// a multiple of 8) gets a lane and a record; the run length (<= 7) rides in bits [22,25) of w2.
+// Should the walk nevertheless come to stand inside a run -- or on one whose first hit does not
+// count -- the event is "virtual": LIVE | DEFER, evaluated by anchor_lookup() when taken.
+// need_pos: prediction mode, where an anchor at reference position 0 counts as none (:604).
+constexpr uint32_t HIT_RUN_SHIFT = 22;
+struct Event { int j, qi, a_pos; uint32_t w2, w3; };
+template <class W, class LI, class LU>
+LZ_HD Event next_event(W& w, const LI& r_p, const LU& r_pos, const LU& r_w2, const LU& r_w3, int i0, int lim, bool need_pos)
+{
+    typename W::template Lanes<int> c1, c2;
+    LZ_EACH(w, ln)
+    {
+        const int p = r_p[ln];
+        const uint32_t w2 = r_w2[ln];
+        const int run = (int)((w2 >> HIT_RUN_SHIFT) & 7u);
+        const bool counts = (w2 & HIT_LIVE) && (!need_pos || (w2 & HIT_DEFER) || r_pos[ln] != 0u);
+        const bool first = p >= i0 && counts;
+        c1[ln] = first && p < lim;
+        // rare: the walk stands inside the run, or the run's first hit does not count
+        c2[ln] = !first && run > 0 && p + run >= i0;
+    }
+    const uint32_t vm1 = w.ballot(c1), vm2 = w.ballot(c2);
+    Event o;
+    o.j = -1; o.qi = 0x7FFFFFFF; o.a_pos = 0; o.w2 = 0; o.w3 = 0;
+    if (vm2 && (!vm1 || (vm2 & (0u - vm2)) < (vm1 & (0u - vm1)))) {
+        const int j2 = ctz32(vm2);
+        const int p2 = w.get(r_p, j2);
+        const int e = p2 + 1 > i0 ? p2 + 1 : i0;
+        if (e < lim) { o.j = j2; o.qi = e; o.w2 = HIT_LIVE | HIT_DEFER; }
+        // (e >= lim: the records are in position order, so nothing else lies below lim either)
+    } else if (vm1) {
+        o.j = ctz32(vm1);
+        o.qi = w.get(r_p, o.j);
+        o.w2 = w.get(r_w2, o.j);
+        o.w3 = w.get(r_w3, o.j);
+        o.a_pos = (int)w.get(r_pos, o.j);
+    }
+    return o;
+}
+
 // ---- the whole pair.
 //
 // Three nested granularities:
@@ -763,8 +816,9 @@ LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q,
 //          along the diagonals of the prediction window.
 // `list` is 32 uint16 of per-warp scratch (shared memory on the device).
 template <class W, class PT>
-LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* list)
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc)
 {
+    uint16_t* list = sc->list;
     ParseState s;
     s.i = 0; s.pred = -1; s.lit = 0;
     s.rs = -1; s.re = 0; s.kept_end = 0;
@@ -777,11 +831,11 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
     int spec_i0 = -1, spec_K1 = 0, spec_ks = 64;   // speculative seed record of the match just taken
     int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
-    typename W::template Lanes<uint32_t> hm[LZ_WIN_WORDS], r_pos, r_w2, r_w3;
+    typename W::template Lanes<uint32_t> r_pos, r_w2, r_w3;
     typename W::template Lanes<int> r_p;
     LZ_EACH(w, ln)
     {
-        for (int q = 0; q < LZ_WIN_WORDS; ++q) hm[q][ln] = 0;
+        for (int q = 0; q < LZ_WIN_WORDS; ++q) sc->hm[q][ln] = 0;
         r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF;
     }
 
@@ -829,20 +883,22 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
                             const int nv = win_end - pos0;
                             if (nv < 32) m &= low_mask32(nv);
                         }
-                        hm[q][ln] = m;
+                        sc->hm[q][ln] = m;
                     }
                 }
             }
-            // ---- new batch: the first <= 32 hits at or after i0
+            // ---- new batch: the first <= 32 hit runs at or after i0
             typename W::template Lanes<int> cnt, pre;
             LZ_EACH(w, ln)
             {
                 int c = 0;
+                LZ_ROLLED
                 for (int q = 0; q < LZ_WIN_WORDS; ++q) {
                     const int rel = i0 - (win_base + LZ_WIN_LANE * ln + 32 * q);
-                    if (rel >= 32) hm[q][ln] = 0;                        // behind the walk: never needed again
-                    else if (rel > 0) hm[q][ln] &= ~low_mask32(rel);
-                    c += popc32(hm[q][ln]);
+                    if (rel >= 32) sc->hm[q][ln] = 0;                        // behind the walk: never needed again
+                    else if (rel > 0) sc->hm[q][ln] &= ~low_mask32(rel);
+                    const uint32_t m = sc->hm[q][ln];
+                    c += popc32(m & ~(m & (m << 1) & ~0x01010101u));     // first positions of runs
                 }
                 cnt[ln] = c;
             }
@@ -851,10 +907,15 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             LZ_EACH(w, ln)
             {
                 int idx = pre[ln];
+                LZ_ROLLED
                 for (int q = 0; q < LZ_WIN_WORDS && idx < 32; ++q) {
-                    uint32_t m = hm[q][ln];
+                    const uint32_t hmw = sc->hm[q][ln];
+                    const uint32_t sec = hmw & (hmw << 1) & ~0x01010101u;
+                    uint32_t m = hmw & ~sec;
                     while (m && idx < 32) {
-                        list[idx++] = (uint16_t)(LZ_WIN_LANE * ln + 32 * q + ctz32(m));
+                        const int b = ctz32(m);
+                        const uint32_t follow = b < 31 ? ~(sec >> (b + 1)) : 1u;     // run: sec bits right behind b
+                        list[idx++] = (uint16_t)((LZ_WIN_LANE * ln + 32 * q + b) | (ctz32(follow) << 12));
                         m &= m - 1u;
                     }
                 }
@@ -864,16 +925,21 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
             lz_batches++; lz_hits += b_cnt;
 #endif
-            LZ_EACH(w, ln) r_p[ln] = ln < b_cnt ? win_base + (int)list[ln] : 0x7FFFFFFF;
+            typename W::template Lanes<int> r_run;
+            LZ_EACH(w, ln)
+            {
+                r_p[ln] = ln < b_cnt ? win_base + (int)(list[ln] & 0xFFFu) : 0x7FFFFFFF;
+                r_run[ln] = ln < b_cnt ? (int)(list[ln] >> 12) : 0;
+            }
             w.sync();
-            b_cover = total <= 32 ? win_end : w.get(r_p, 31) + 1;
+            b_cover = total <= 32 ? win_end : w.get(r_p, 31) + w.get(r_run, 31) + 1;
             // three stages, each entered by the whole warp (sync = reconvergence point): lanes take
             // different numbers of probe / scan iterations and must not stay split afterwards
             LZ_EACH(w, ln)
             {
                 uint32_t a = 0, b = 0;
                 if (ln < b_cnt) hit_probe(pv, P, r_p[ln], a, b);
-                r_pos[ln] = a; r_w2[ln] = b; r_w3[ln] = 0;
+                r_pos[ln] = a; r_w2[ln] = b | ((uint32_t)r_run[ln] << HIT_RUN_SHIFT); r_w3[ln] = 0;
             }
             w.sync();
             LZ_EACH(w, ln)
@@ -892,8 +958,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
                         const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
                         const int si0 = r_p[ln] + adv, sP0 = (int)r_pos[ln] + adv;
                         int idx = ln + 1;
-                        while (idx < b_cnt && win_base + (int)list[idx] < si0) ++idx;
-                        int K = idx < b_cnt ? win_base + (int)list[idx] - si0 : b_cover - 1 - si0;
+                        while (idx < b_cnt && win_base + (int)(list[idx] & 0xFFFu) < si0) ++idx;
+                        int K = idx < b_cnt ? win_base + (int)(list[idx] & 0xFFFu) - si0 : b_cover - 1 - si0;
                         if (K > P.mqd) K = P.mqd;
                         const int ks = spec_first_seed(pv, P, si0, sP0, K);
                         if (ks >= 0) r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
@@ -912,15 +978,12 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
         // general code below, which re-derives the same step.
         if (PT::kSpecSeeds && (s.pred < 0 || (s.lit == 0 && i0 == spec_i0 && spec_K1 > 0))) {
-            typename W::template Lanes<int> c;
-            LZ_EACH(w, ln) c[ln] = r_p[ln] >= i0 && (r_w2[ln] & HIT_LIVE);
-            const uint32_t vm = w.ballot(c);
-            const int j = vm ? ctz32(vm) : 0;
-            const int qi = vm ? w.get(r_p, j) : 0x7FFFFFFF;
+            const Event ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
+            const int qi = ev.qi;
             const int ka = qi - i0;
-            const uint32_t w2 = w.get(r_w2, j);
-            const int a_pos = (int)w.get(r_pos, j);
-            bool plain = vm && (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
+            const uint32_t w2 = ev.w2;
+            const int a_pos = ev.a_pos;
+            bool plain = (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
             if (s.pred >= 0) {
                 if (ka > P.mqd) {
                     plain = false;
@@ -938,7 +1001,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
                 }
             }
             if (plain) {
-                const uint32_t w3 = w.get(r_w3, j);
+                const uint32_t w3 = ev.w3;
                 const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
                 const int kept_end = keep ? s.re : s.kept_end;
                 const int run = qi - kept_end;
@@ -968,18 +1031,15 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
 
         if (s.pred < 0) {
             // ---- no prediction (:507-532): the next event is the next live anchor record
-            typename W::template Lanes<int> c;
-            LZ_EACH(w, ln) c[ln] = r_p[ln] >= i0 && (r_w2[ln] & HIT_LIVE);
-            const uint32_t vm = w.ballot(c);
-            if (!vm) {
+            const Event ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
+            if (ev.j < 0) {
                 s.lit += b_cover - i0;
                 s.i = b_cover;
                 continue;
             }
-            const int j = ctz32(vm);
-            const int qi = w.get(r_p, j);
-            uint32_t w2 = w.get(r_w2, j), w3 = w.get(r_w3, j);
-            int a_pos = (int)w.get(r_pos, j), a_len = (int)(w2 & 63u);
+            const int qi = ev.qi;
+            uint32_t w2 = ev.w2, w3 = ev.w3;
+            int a_pos = ev.a_pos, a_len = (int)(w2 & 63u);
             if (w2 & HIT_DEFER) {
                 uint32_t lo, hi, nm;
                 ext3(pv.q, qi, lo, hi, nm);
@@ -1007,12 +1067,9 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         const bool use_spec = PT::kSpecSeeds && lit0 == 0 && i0 == spec_i0 && spec_K1 > 0;
         if (use_spec && n > spec_K1) n = spec_K1;
         // the first anchor record inside the chunk that counts here (position 0 == "none", :604)
-        typename W::template Lanes<int> c;
-        LZ_EACH(w, ln)
-            c[ln] = r_p[ln] >= i0 && r_p[ln] < i0 + n && (r_w2[ln] & HIT_LIVE) && ((r_w2[ln] & HIT_DEFER) || r_pos[ln] != 0u);
-        const uint32_t vm = w.ballot(c);
-        const int ja = vm ? ctz32(vm) : -1;
-        const int ka = ja >= 0 ? w.get(r_p, ja) - i0 : n;
+        const Event eva = next_event(w, r_p, r_pos, r_w2, r_w3, i0, i0 + n, true);
+        const int ja = eva.j;
+        const int ka = ja >= 0 ? eva.qi - i0 : n;
         const int ns = ja >= 0 ? ka + 1 : n;          // positions examined by this step
 
         // seeds: runs of >= msl equal bases along the diagonals [d_lo, d_hi) of the window
@@ -1048,9 +1105,9 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
             }
             uint32_t w2 = 0, w3 = 0;
             if (ja >= 0 && k == ka) {
-                w2 = w.get(r_w2, ja);
-                w3 = w.get(r_w3, ja);
-                int a_pos = (int)w.get(r_pos, ja), a_len = (int)(w2 & 63u);
+                w2 = eva.w2;
+                w3 = eva.w3;
+                int a_pos = eva.a_pos, a_len = (int)(w2 & 63u);
                 if (w2 & HIT_DEFER) {
                     uint32_t lo, hi, nm;
                     ext3(pv.q, qi, lo, hi, nm);
@@ -1103,6 +1160,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, uint16_t* lis
         const int n = s.lit + (Dq - s.i);
         FwdStream ts{&pv, s.i - s.lit, s.pred - s.lit - P.msl};
         int last = 0, mt = 0;
+        LZ_ROLLED
         for (int base = 0; base < n; base += 1024) {
             typename W::template Lanes<uint32_t> eq;
             typename W::template Lanes<int> hi, c;

@@ -19,7 +19,11 @@
 // rarely executed warp-cooperative routines: kept out of line so that the hot loop of the
 // parse kernel stays inside the instruction cache
 #define LZ_COLD __host__ __device__ __noinline__
+// the parse kernel is bound by instruction issue AND sits at the edge of the instruction cache:
+// loops outside the innermost bit loops are kept rolled
+#define LZ_ROLLED _Pragma("unroll 1")
 #else
+#define LZ_ROLLED
 #define LZ_HD inline
 #define LZ_D inline
 #define LZ_COLD inline

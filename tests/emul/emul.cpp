@@ -78,7 +78,7 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
     std::atomic<uint64_t> next{0};
     auto worker = [&]() {
         HostWarp w;
-        uint16_t list[32];
+        WarpScratch scratch;
         HostIndex ix;
         for (;;) {
             uint64_t j = next.fetch_add(1);
@@ -95,8 +95,8 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 pv.table = ix.table.data(); pv.tbits = ix.tbits;
                 // same dispatch as launch_parse(): compile-time defaults or run-time parameters
                 PairResult res;
-                if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, list); }
-                else res = parse_pair(w, pv, P, list);
+                if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch); }
+                else res = parse_pair(w, pv, P, &scratch);
                 out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
                 ++k;
             };

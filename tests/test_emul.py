@@ -55,3 +55,17 @@ def test_speculative_seed_records_agree_with_diagonal_scan(emul):
     emul.lib.lzani_emul_spec_stats(C.byref(used), C.byref(bad))
     assert used.value > 1000, "speculative records were not exercised"
     assert bad.value == 0
+
+
+@pytest.mark.parametrize("seed", list(range(100, 112)))
+def test_kernel_source_randomized_differential(emul, seed):
+    """Default parameters (speculative seed records, hit-run records, fast path all active) on
+    families of varying divergence plus a low-complexity tandem-repeat sequence."""
+    rng = np.random.default_rng(seed)
+    names, seqs = synth.families(2, 4, 2000, 7000, seed=seed, d_lo=0.0 if seed % 3 == 0 else 0.01,
+                                 d_hi=[0.05, 0.15, 0.35][seed % 3], block=(100, 500))
+    rep = np.tile(rng.integers(0, 4, size=int(rng.integers(1, 9)), dtype=np.uint8), 400)[:1500]
+    seqs = list(seqs) + [np.concatenate([seqs[0][:800], rep, seqs[1][:700]])]
+    names = list(names) + ["rep"]
+    ss = hostio.SeqSet(names, seqs)
+    assert np.array_equal(emul.run_rows(ss, None, threads=4), Oracle().run_rows(ss, None, threads=4))
