@@ -469,7 +469,7 @@ struct WarpScratch {
     uint16_t list[32];
 };
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
-static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0;   // TEST ONLY counters (tests/emul)
+static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0, lz_why[12] = {0};   // TEST ONLY counters (tests/emul)
 #endif
 template <class PT>
 LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
@@ -1000,6 +1000,18 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     plain = plain && ka < spec_K1 && spec_ks > ka && a_pos != 0 && dist > P.mrd;
                 }
             }
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+            if (!plain) {   // TEST ONLY: why the fast path was left
+                if (ev.j < 0) lz_why[0]++;
+                else if (w2 & HIT_DEFER) lz_why[1]++;
+                else if (!(w2 & HIT_FWD)) lz_why[2]++;
+                else if (s.pred >= 0 && ka > P.mqd) lz_why[3]++;
+                else if (s.pred >= 0 && ka >= spec_K1) lz_why[4]++;
+                else if (s.pred >= 0 && spec_ks <= ka) lz_why[5]++;
+                else if (s.pred >= 0 && a_pos == 0) lz_why[6]++;
+                else lz_why[7]++;          // close anchor
+            }
+#endif
             if (plain) {
                 const uint32_t w3 = ev.w3;
                 const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
@@ -1026,8 +1038,14 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
 #endif
                     continue;
                 }
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                lz_why[8]++;               // backward record not usable
+#endif
             }
         }
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+        else lz_why[9]++;                  // no speculative record for this state
+#endif
 
         if (s.pred < 0) {
             // ---- no prediction (:507-532): the next event is the next live anchor record
