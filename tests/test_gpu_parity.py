@@ -124,3 +124,45 @@ def test_properties_at_bench_scale():
         assert np.array_equal(got, want)
     finally:
         m.close()
+
+
+def test_sparse_filter_style_pair_list_config4():
+    """BASELINE configs[3] shape at test size: a --flt-kmerdb-style sparse pair list (within-family
+    pairs plus a few cross-family decoys, unsorted inside a row as filter rows are) through the CSR
+    entry point, against the oracle."""
+    names, seqs = synth.families(6, 6, 5000, 9000, seed=41, d_lo=0.02, d_hi=0.25, block=(200, 900))
+    ss = hostio.SeqSet(names, seqs)
+    n = len(ss)
+    rng = np.random.default_rng(41)
+    off, q = [0], []
+    for r in range(n):
+        fam = r // 6
+        ids = [x for x in range(fam * 6, fam * 6 + 6) if x != r and rng.random() < 0.8]
+        ids += [int(x) for x in rng.integers(0, n, size=2) if x != r and x // 6 != fam]
+        rng.shuffle(ids)
+        q.extend(ids)
+        off.append(len(q))
+    off, q = np.array(off, np.uint64), np.array(q, np.uint32)
+    m = lz.Matcher(device=0)
+    try:
+        m.set_sequences(ss)
+        got = m.run(off, q)
+    finally:
+        m.close()
+    want = Oracle().run_rows(ss, None, row_off=off, q_ids=q)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("params", [mg.LONGP, None])
+def test_megabase_genomes_config5(params):
+    """BASELINE configs[4] shape at test size: bacterial-scale (1.2 Mb) related genomes with the
+    long-genome parameter set (hashed bitmap, 64-bit keys, 2^23-slot tables) and with the defaults
+    (dense hits, long matches, long extensions), against the oracle."""
+    rng = np.random.default_rng(55)
+    root = rng.integers(0, 4, size=1_200_000, dtype=np.uint8)
+    seqs = [root, synth._mutate(rng, root, 0.04, block=(5000, 50000), p_block=1.0),
+            synth._mutate(rng, root, 0.12, block=(5000, 50000), p_block=1.0)]
+    ss = hostio.SeqSet(["root", "m4", "m12"], seqs)
+    got, _ = run_gpu(ss, params)
+    want = Oracle().run_rows(ss, params)
+    assert np.array_equal(got, want), f"{got.tolist()} vs {want.tolist()}"
