@@ -460,7 +460,7 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
     return r;
 }
 constexpr int SPEC_MAX_K = 57;
-constexpr int LZ_WIN_WORDS = 4;                    // hit-mask words per lane and window
+constexpr int LZ_WIN_WORDS = 8;                    // hit-mask words per lane and window (8192 positions)
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 // per-warp scratch (shared memory on the device): the hit masks of the current window, one column
 // per lane, and the hit list of the current batch
@@ -915,7 +915,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     while (m && idx < 32) {
                         const int b = ctz32(m);
                         const uint32_t follow = b < 31 ? ~(sec >> (b + 1)) : 1u;     // run: sec bits right behind b
-                        list[idx++] = (uint16_t)((LZ_WIN_LANE * ln + 32 * q + b) | (ctz32(follow) << 12));
+                        list[idx++] = (uint16_t)((LZ_WIN_LANE * ln + 32 * q + b) | (ctz32(follow) << 13));
                         m &= m - 1u;
                     }
                 }
@@ -928,8 +928,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             typename W::template Lanes<int> r_run;
             LZ_EACH(w, ln)
             {
-                r_p[ln] = ln < b_cnt ? win_base + (int)(list[ln] & 0xFFFu) : 0x7FFFFFFF;
-                r_run[ln] = ln < b_cnt ? (int)(list[ln] >> 12) : 0;
+                r_p[ln] = ln < b_cnt ? win_base + (int)(list[ln] & 0x1FFFu) : 0x7FFFFFFF;
+                r_run[ln] = ln < b_cnt ? (int)(list[ln] >> 13) : 0;
             }
             w.sync();
             b_cover = total <= 32 ? win_end : w.get(r_p, 31) + w.get(r_run, 31) + 1;
@@ -958,8 +958,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
                         const int si0 = r_p[ln] + adv, sP0 = (int)r_pos[ln] + adv;
                         int idx = ln + 1;
-                        while (idx < b_cnt && win_base + (int)(list[idx] & 0xFFFu) < si0) ++idx;
-                        int K = idx < b_cnt ? win_base + (int)(list[idx] & 0xFFFu) - si0 : b_cover - 1 - si0;
+                        while (idx < b_cnt && win_base + (int)(list[idx] & 0x1FFFu) < si0) ++idx;
+                        int K = idx < b_cnt ? win_base + (int)(list[idx] & 0x1FFFu) - si0 : b_cover - 1 - si0;
                         if (K > P.mqd) K = P.mqd;
                         const int ks = spec_first_seed(pv, P, si0, sP0, K);
                         if (ks >= 0) r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
