@@ -112,6 +112,18 @@ int lzani_run(lzani_ctx* ctx, uint32_t n_refs, const uint64_t* row_off, const ui
 int lzani_run_rows(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
                    const uint32_t* q_ids, lzani_result_t* out);
 
+/* Replaces `parser.get_parsing()` (parser.h:253, calc_regions parser.cpp:786-837) as used for
+ * --out-alignment (lz_matcher.cpp:226-227): the same rows as lzani_run_rows() and, besides out[],
+ * the kept regions of every pair in CSR form: the regions of the k-th pair are
+ * regions[region_off[k] .. region_off[k+1]), sorted the way calc_regions sorts them (length
+ * descending, then seq_start).  region_off has n_pairs + 1 entries.  *n_regions receives the total;
+ * when it exceeds regions_cap nothing is written to regions[] / region_off[] and LZANI_ERR_NOMEM is
+ * returned: call again with a buffer of at least *n_regions entries.  Reference coordinates are
+ * those of seq_ref (forward | 2*mrd N | reverse complement, parser.cpp:16-34), as in the reference. */
+int lzani_run_rows_regions(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
+                           const uint32_t* q_ids, lzani_result_t* out, uint64_t* region_off,
+                           lzani_region_t* regions, uint64_t regions_cap, uint64_t* n_regions);
+
 /* Device-resident variant used to time the kernels alone: runs the same rows `repeat`
  * times back to back without copying results to the host; the last pass's results are
  * left on the device and copied to `out` only if out != NULL. */

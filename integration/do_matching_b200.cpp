@@ -57,10 +57,6 @@ void CLZMatcher::do_matching()
 {
     if (params.verbosity_level >= 1)
         cerr << "All2all sparse (B200)" << endl;
-    if (f_alignment) {
-        cerr << "lzani-b200: --out-alignment is not covered by the B200 path yet (SURVEY 8f-2)" << endl;
-        exit(1);
-    }
 
     const uint32_t n = (uint32_t)seq_reservoir.size();
     results.clear();
@@ -91,8 +87,10 @@ void CLZMatcher::do_matching()
     const bool dense = filter.is_empty();
     const std::vector<int> devs = devices_from_env();
     const uint32_t G = (uint32_t)devs.size();
-    // rows per submit: bounded result buffers, and a progress tick between submits
-    const uint64_t max_pairs_per_call = 16ull << 20;
+    // rows per submit: bounded result buffers, and a progress tick between submits.  With
+    // --out-alignment every pair also returns its region records (parser.get_parsing(),
+    // lz_matcher.cpp:226-227): smaller submits keep that buffer bounded.
+    const uint64_t max_pairs_per_call = f_alignment ? (1ull << 20) : (16ull << 20);
 
     std::atomic<uint64_t> done_rows{0};
     std::vector<std::thread> workers;
@@ -106,6 +104,9 @@ void CLZMatcher::do_matching()
             std::vector<uint32_t> rows, q_ids;
             std::vector<uint64_t> row_off;
             std::vector<lzani_result_t> out;
+            std::vector<uint64_t> region_off;
+            std::vector<lzani_region_t> regions;
+            std::vector<region_t> parsing;
             uint32_t r = g;
             while (r < n) {
                 rows.clear(); q_ids.clear(); row_off.assign(1, 0);
@@ -121,9 +122,23 @@ void CLZMatcher::do_matching()
                     r += G;
                 }
                 out.resize(pairs);
-                const int rc = lzani_run_rows(ctx, (uint32_t)rows.size(), rows.data(), dense ? nullptr : row_off.data(),
-                                              dense ? nullptr : q_ids.data(), out.data());
-                if (rc != LZANI_OK) die("lzani_run_rows", ctx);
+                if (f_alignment) {
+                    region_off.resize(pairs + 1);
+                    if (regions.size() < 1024) regions.resize(1024);
+                    for (;;) {
+                        uint64_t need = 0;
+                        const int rc = lzani_run_rows_regions(ctx, (uint32_t)rows.size(), rows.data(), dense ? nullptr : row_off.data(),
+                                                              dense ? nullptr : q_ids.data(), out.data(), region_off.data(),
+                                                              regions.data(), regions.size(), &need);
+                        if (rc == LZANI_ERR_NOMEM && need > regions.size()) { regions.resize(need + need / 8); continue; }
+                        if (rc != LZANI_OK) die("lzani_run_rows_regions", ctx);
+                        break;
+                    }
+                } else {
+                    const int rc = lzani_run_rows(ctx, (uint32_t)rows.size(), rows.data(), dense ? nullptr : row_off.data(),
+                                                  dense ? nullptr : q_ids.data(), out.data());
+                    if (rc != LZANI_OK) die("lzani_run_rows", ctx);
+                }
                 for (size_t j = 0; j < rows.size(); ++j) {
                     const uint32_t ref = rows[j];
                     vec_id_results_t res_row;
@@ -134,6 +149,14 @@ void CLZMatcher::do_matching()
                         if (dense) { q = (uint32_t)(k - a); if (q >= ref) ++q; }
                         else q = q_ids[k];
                         res_row.emplace_back(q, results_t(out[k].sym_in_matches, out[k].sym_in_literals, out[k].no_components));
+                        if (f_alignment) {
+                            parsing.clear();
+                            for (uint64_t e = region_off[k]; e < region_off[k + 1]; ++e) {
+                                const lzani_region_t& g = regions[e];
+                                parsing.emplace_back(g.ref_start, g.ref_end, g.seq_start, g.seq_end, g.num_matches, g.num_mismatches);
+                            }
+                            store_alignment(ref, q, parsing);       // the reference's own writer (lz_matcher.cpp:102-169)
+                        }
                     }
                     std::sort(res_row.begin(), res_row.end());
                     results[ref] = std::move(res_row);       // each row is written by exactly one thread

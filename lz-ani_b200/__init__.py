@@ -35,7 +35,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
     srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "capi.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "simt.h")] + [
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "regions.h", "simt.h")] + [
         os.path.join(ROOT, "include", "lzani_b200.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
@@ -78,6 +78,7 @@ def load_library() -> C.CDLL:
     lib.lzani_run.argtypes = [vp, u32, vp, vp, vp]
     lib.lzani_run_rows.argtypes = [vp, u32, vp, vp, vp, vp]
     lib.lzani_run_rows_resident.argtypes = [vp, u32, vp, vp, vp, C.c_int, vp]
+    lib.lzani_run_rows_regions.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, u64, vp]
     lib.lzani_get_timing.argtypes = [vp, C.POINTER(TimingStruct)]
     lib.lzani_set_index_budget.argtypes = [vp, u64]
     lib.lzani_last_error.argtypes = [vp]
@@ -175,5 +176,35 @@ class Matcher:
                         "lzani_run_rows")
         return out
 
+
+def _run_rows_regions(self, rows, row_off=None, q_ids=None, cap: int = 1 << 16):
+    """Counts plus the kept regions of every pair (what --out-alignment needs; replaces
+    CParser::get_parsing, parser.cpp:786-837).  Returns (out, region_off, regions[n, 6]) with the
+    region columns ref_start, ref_end, seq_start, seq_end, num_matches, num_mismatches."""
+    rows = np.ascontiguousarray(rows, dtype=np.uint32)
+    if q_ids is None:
+        n_pairs = rows.size * max(self.n - 1, 0)
+        off_p = q_p = None
+    else:
+        row_off = np.ascontiguousarray(row_off, dtype=np.uint64)
+        q_ids = np.ascontiguousarray(q_ids, dtype=np.uint32)
+        n_pairs = int(row_off[-1] - row_off[0])
+        off_p, q_p = row_off.ctypes.data, q_ids.ctypes.data
+    out = np.zeros((n_pairs, 3), dtype=np.int32)
+    region_off = np.zeros(n_pairs + 1, dtype=np.uint64)
+    for _ in range(2):
+        regions = np.zeros((max(cap, 1), 6), dtype=np.int32)
+        n_reg = C.c_uint64(0)
+        rc = self.lib.lzani_run_rows_regions(self.h, rows.size, rows.ctypes.data, off_p, q_p, out.ctypes.data,
+                                             region_off.ctypes.data, regions.ctypes.data, cap, C.byref(n_reg))
+        if rc == 4 and n_reg.value > cap:      # LZANI_ERR_NOMEM: the library says how many it needs
+            cap = int(n_reg.value)
+            continue
+        self._check(rc, "lzani_run_rows_regions")
+        return out, region_off, regions[: int(n_reg.value)].copy()
+    raise LzaniError("lzani_run_rows_regions: region count changed between calls")
+
+
+Matcher.run_rows_regions = _run_rows_regions
 
 from .sharding import shard_rows  # noqa: E402,F401

@@ -47,6 +47,8 @@ struct lzani_ctx {
     uint32_t* d_q_ids = nullptr; uint64_t q_cap = 0;
     void* d_out = nullptr; uint64_t out_cap = 0;
     unsigned long long* d_counter = nullptr;
+    DevRegion* d_regs = nullptr; uint64_t regs_cap = 0;     // regions kernel (--out-alignment)
+    unsigned long long* d_reg_counter = nullptr;
 
     cudaEvent_t ev[8]{};
     lzani_timing_t timing{};
@@ -136,6 +138,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     LZ_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto& ev : c->ev) LZ_CUDA(c, cudaEventCreate(&ev));
     LZ_CUDA(c, cudaMalloc((void**)&c->d_counter, sizeof(unsigned long long)));
+    LZ_CUDA(c, cudaMalloc((void**)&c->d_reg_counter, sizeof(unsigned long long)));
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
     return LZANI_OK;
 }
@@ -149,6 +152,7 @@ extern "C" void lzani_destroy(lzani_ctx* c)
         cudaFree(c->d_bitmap); cudaFree(c->d_table);
         cudaFree(c->d_row_ref); cudaFree(c->d_row_idx); cudaFree(c->d_row_off); cudaFree(c->d_blk_base);
         cudaFree(c->d_q_ids); cudaFree(c->d_out); cudaFree(c->d_counter);
+        cudaFree(c->d_regs); cudaFree(c->d_reg_counter);
         for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
         if (c->stream) cudaStreamDestroy(c->stream);
     }
@@ -246,8 +250,15 @@ struct RowPlan {
 
 // The whole hot path for a set of reference rows.  `repeat` > 1 re-runs index build + parse
 // with everything resident (bench "value" leg).
+struct RegionReq {          // lzani_run_rows_regions: where the regions go
+    uint64_t* region_off;
+    lzani_region_t* regions;
+    uint64_t cap;
+    uint64_t* n_regions;
+};
+
 int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off_in,
-                  const uint32_t* q_ids, int repeat, lzani_result_t* out, bool copy_out)
+                  const uint32_t* q_ids, int repeat, lzani_result_t* out, bool copy_out, const RegionReq* rq = nullptr)
 {
     if (!c) return LZANI_ERR_ARG;
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
@@ -315,6 +326,12 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         uint8_t* p = (uint8_t*)c->d_out;
         if (int rc = ensure(c, p, cap_bytes, n_pairs * sizeof(lzani_result_t))) return rc;
         c->d_out = p; c->out_cap = cap_bytes;
+    }
+
+    if (rq) {
+        if (!rq->n_regions || (rq->cap && (!rq->regions || !rq->region_off))) return fail(c, LZANI_ERR_ARG, "region buffers == NULL");
+        if (int rc = ensure(c, c->d_regs, c->regs_cap, rq->cap ? rq->cap : 1)) return rc;
+        LZ_CUDA(c, cudaMemsetAsync(c->d_reg_counter, 0, sizeof(unsigned long long), c->stream));
     }
 
     // ---- batches of consecutive rows under the index budget
@@ -389,9 +406,15 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                                           nb, h_blk[nb], P, c->d_bitmap, c->d_table));
             LZ_CUDA(c, cudaEventRecord(c->ev[4], st));
             LZ_CUDA(c, cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned long long), st));
-            LZ_CUDA(c, launch_parse(st, grid, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
-                                    c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a], row_off[b.b], P,
-                                    c->d_bitmap, c->d_table, c->d_counter, c->d_out));
+            if (rq)
+                LZ_CUDA(c, launch_parse_regions(st, grid, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
+                                                c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a],
+                                                row_off[b.b], P, c->d_bitmap, c->d_table, c->d_counter, c->d_out,
+                                                c->d_regs, c->d_reg_counter, rq->cap));
+            else
+                LZ_CUDA(c, launch_parse(st, grid, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
+                                        c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a], row_off[b.b], P,
+                                        c->d_bitmap, c->d_table, c->d_counter, c->d_out));
             LZ_CUDA(c, cudaEventRecord(c->ev[5], st));
             LZ_CUDA(c, cudaStreamSynchronize(st));
             T.h2d_ms += ms_between(c->ev[2], c->ev[3]);
@@ -414,6 +437,32 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
     T.q_bases = q_bases * (uint64_t)repeat;
     T.r_bases = r_bases * (uint64_t)repeat;
     c->timing = T;
+    if (rq) {
+        // regions: bring them back, group by pair (counting sort), order each group like calc_regions
+        unsigned long long total = 0;
+        LZ_CUDA(c, cudaMemcpy(&total, c->d_reg_counter, sizeof(total), cudaMemcpyDeviceToHost));
+        *rq->n_regions = total;
+        if (total > rq->cap) return fail(c, LZANI_ERR_NOMEM, "regions buffer too small: " + std::to_string(total) + " regions");
+        std::vector<DevRegion> h(total);
+        if (total) LZ_CUDA(c, cudaMemcpy(h.data(), c->d_regs, sizeof(DevRegion) * total, cudaMemcpyDeviceToHost));
+        c->timing.d2h_bytes += sizeof(DevRegion) * total;
+        std::vector<uint64_t> off(n_pairs + 1, 0);
+        for (const DevRegion& d : h) ++off[d.pair + 1];
+        for (uint64_t k = 0; k < n_pairs; ++k) off[k + 1] += off[k];
+        std::vector<uint64_t> cur(off.begin(), off.end() - 1);
+        for (const DevRegion& d : h) {
+            lzani_region_t& o = rq->regions[cur[d.pair]++];
+            o.ref_start = d.g.ref_start; o.ref_end = d.g.ref_end; o.seq_start = d.g.seq_start; o.seq_end = d.g.seq_end;
+            o.num_matches = d.g.num_matches; o.num_mismatches = d.g.num_mismatches;
+        }
+        for (uint64_t k = 0; k < n_pairs; ++k)
+            std::stable_sort(rq->regions + off[k], rq->regions + off[k + 1], [](const lzani_region_t& a, const lzani_region_t& b) {
+                const int la = a.seq_end - a.seq_start, lb = b.seq_end - b.seq_start;     // parser.cpp:828-833
+                if (la != lb) return la > lb;
+                return a.seq_start < b.seq_start;
+            });
+        memcpy(rq->region_off, off.data(), sizeof(uint64_t) * (n_pairs + 1));
+    }
     return LZANI_OK;
 }
 
@@ -431,6 +480,14 @@ extern "C" int lzani_run_rows(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref
                               const uint32_t* q_ids, lzani_result_t* out)
 {
     return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, 1, out, true);
+}
+
+extern "C" int lzani_run_rows_regions(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
+                                      const uint32_t* q_ids, lzani_result_t* out, uint64_t* region_off,
+                                      lzani_region_t* regions, uint64_t regions_cap, uint64_t* n_regions)
+{
+    const RegionReq rq{region_off, regions, regions_cap, n_regions};
+    return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, 1, out, true, &rq);
 }
 
 extern "C" int lzani_run_rows_resident(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids,

@@ -122,6 +122,70 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 }
 
 // ------------------------------------------------------------------------------------------
+// K3r.  The same parse with the region fold switched on (regions.h): besides the counts, every kept
+// region of every pair is appended to `regs` (any order; the host groups and sorts them the way
+// calc_regions does).  Used for --out-alignment only; no speculative records, no fast path.
+struct DevRegionOut {
+    DevRegion* buf;
+    unsigned long long* counter;
+    unsigned long long cap;
+    unsigned long long pair;
+    int lane;
+    __device__ __forceinline__ void emit(const RegionRec& g)
+    {
+        if (lane == 0) {
+            const unsigned long long idx = atomicAdd(counter, 1ull);
+            if (idx < cap) { DevRegion d; d.pair = pair; d.g = g; buf[idx] = d; }
+        }
+    }
+};
+
+template <class PT>
+__global__ void __launch_bounds__(LZ_PARSE_THREADS)
+k_parse_regions(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
+                const uint32_t* __restrict__ row_ref, const RefIndex* __restrict__ row_idx,
+                const uint64_t* __restrict__ row_off, uint32_t n_rows, const uint32_t* __restrict__ q_ids,
+                uint64_t pair_begin, uint64_t pair_end, PT P, const uint32_t* __restrict__ bitmap_pool,
+                const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
+                int3* __restrict__ out, DevRegion* __restrict__ regs, unsigned long long* __restrict__ reg_counter,
+                unsigned long long reg_cap)
+{
+    DevWarp w((int)(threadIdx.x & 31u));
+    __shared__ WarpScratch scratch[LZ_PARSE_THREADS / 32];
+    WarpScratch* sc = &scratch[threadIdx.x >> 5];
+    for (;;) {
+        unsigned long long k = 0;
+        if (w.lane == 0) k = atomicAdd(counter, 1ull);
+        k = __shfl_sync(0xFFFFFFFFu, k, 0) + pair_begin;
+        if (k >= pair_end) return;
+        const uint32_t j = find_segment<uint64_t>(row_off, n_rows, (uint64_t)k);
+        const uint32_t r = row_ref[j];
+        uint32_t q;
+        if (q_ids) q = q_ids[k];
+        else {
+            q = (uint32_t)(k - row_off[j]);
+            if (q >= r) ++q;
+        }
+        const SeqMeta mr = meta[r], mq = meta[q];
+        const RefIndex ix = row_idx[j];
+        PairView pv;
+        pv.q = recs + mq.q_rec;
+        pv.Dq = (int)mq.len + P.mrd;
+        pv.r = recs + mr.r_rec;
+        pv.Dr = r_form_len((int)mr.len, P.mrd);
+        pv.bitmap = bitmap_pool + ix.bitmap_word;
+        pv.bbits = ix.bbits;
+        pv.table = table_pool + ix.table_slot;
+        pv.tbits = ix.tbits;
+        DevRegionOut ro{regs, reg_counter, reg_cap, k, w.lane};
+        RegionTracker<DevRegionOut> rt;
+        rt.out = &ro;
+        const PairResult res = parse_pair(w, pv, P, sc, rt);
+        if (w.lane == 0) out[k] = make_int3(res.m, res.x, res.n);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // launch wrappers (called by capi.cu)
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* src, const SeqMeta* meta, const uint64_t* rec_base,
                         uint32_t n_seqs, uint64_t n_recs, int mrd, Rec* recs)
@@ -168,6 +232,26 @@ cudaError_t launch_parse(cudaStream_t st, int grid_blocks, const Rec* recs, cons
         k_parse_pairs<Prm><<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(recs, meta, row_ref, row_idx, row_off, n_rows, q_ids,
                                                                  pair_begin, pair_end, P, bitmap_pool, table_pool,
                                                                  counter, reinterpret_cast<int3*>(out));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_parse_regions(cudaStream_t st, int grid_blocks, const Rec* recs, const SeqMeta* meta,
+                                 const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,
+                                 uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint64_t pair_end,
+                                 const Prm& P, const uint32_t* bitmap_pool, const uint64_t* table_pool,
+                                 unsigned long long* counter, void* out, DevRegion* regs,
+                                 unsigned long long* reg_counter, uint64_t reg_cap)
+{
+    if (pair_end <= pair_begin) return cudaSuccess;
+    if (is_default_kernel_params(P)) {
+        const PrmDefault D{P.mrd, P.mqd, P.reg};
+        k_parse_regions<PrmDefault><<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(
+            recs, meta, row_ref, row_idx, row_off, n_rows, q_ids, pair_begin, pair_end, D, bitmap_pool, table_pool, counter,
+            reinterpret_cast<int3*>(out), regs, reg_counter, (unsigned long long)reg_cap);
+    } else
+        k_parse_regions<Prm><<<grid_blocks, LZ_PARSE_THREADS, 0, st>>>(
+            recs, meta, row_ref, row_idx, row_off, n_rows, q_ids, pair_begin, pair_end, P, bitmap_pool, table_pool, counter,
+            reinterpret_cast<int3*>(out), regs, reg_counter, (unsigned long long)reg_cap);
     return cudaGetLastError();
 }
 

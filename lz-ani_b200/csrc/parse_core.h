@@ -21,6 +21,7 @@
 // Everything is written against the warp policy W of simt.h.
 #pragma once
 #include "layout.h"
+#include "regions.h"
 
 namespace lzani {
 
@@ -272,6 +273,143 @@ LZ_COLD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_r
         if (m > best) best = m;
     }
     return best;
+}
+
+// ---- regions kernel only: what compare_ranges (parser.cpp:210-248) would emit for `len` columns of a
+// forward stream, condensed to what the region fold needs (regions.h).
+template <class W>
+LZ_COLD RangeSummary summarize_range(W& w, const FwdStream& st, int len)
+{
+    RangeSummary u;
+    u.first = -1; u.first_run = 0; u.last_end = 0; u.matches = 0;
+    bool growing = false;
+    LZ_ROLLED
+    for (int base = 0; base < len; base += 1024) {
+        typename W::template Lanes<uint32_t> eq;
+        typename W::template Lanes<int> nz, c;
+        LZ_EACH(w, ln)
+        {
+            const int p0 = base + 32 * ln, nv = len - p0;
+            eq[ln] = nv <= 0 ? 0u : (~st.word(p0 >> 5) & low_mask32(nv > 32 ? 32 : nv));
+            nz[ln] = eq[ln] != 0;
+            c[ln] = popc32(eq[ln]);
+        }
+        const uint32_t any = w.ballot(nz);
+        u.matches += w.add_i32(c);
+        if (any) {
+            const int lh = 31 - clz32(any);
+            u.last_end = base + 32 * lh + 32 - clz32(w.get(eq, lh));
+            if (u.first < 0) {
+                const int l0 = ctz32(any);
+                u.first = base + 32 * l0 + ctz32(w.get(eq, l0));
+                growing = true;
+            }
+        }
+        if (growing) {
+            // first column at or after u.first (inside this chunk, below len) that does not match
+            typename W::template Lanes<int> zp;
+            LZ_EACH(w, ln)
+            {
+                const int p0 = base + 32 * ln, nv = len - p0;
+                uint32_t z = nv <= 0 ? 0u : (~eq[ln] & low_mask32(nv > 32 ? 32 : nv));
+                const int rel = u.first - p0;
+                if (rel >= 32) z = 0;
+                else if (rel > 0) z &= ~low_mask32(rel);
+                zp[ln] = z ? p0 + ctz32(z) : 0x7FFFFFFF;
+            }
+            const int mn = w.min_i32(zp);
+            if (mn != 0x7FFFFFFF) { u.first_run = mn - u.first; growing = false; }
+        }
+    }
+    if (growing) u.first_run = len - u.first;
+    return u;
+}
+
+// ---- regions kernel only: the factors compare_ranges_both_ways (parser.cpp:251-374) emits for the gap
+// of `len` query bases ending at qe, fed to the region fold column by column (uniform serial code:
+// the gap is at most mqd+1 long).  Same split rule as both_ways_best() -- the LAST split with the
+// maximal sum -- and the reference's position bookkeeping of the right-hand part (:353-368).
+template <class W, class RS>
+LZ_COLD void both_ways_regions(W& w, const PairView& pv, RS& rt, int qe, int r_left, int r_right, int len)
+{
+    if (len <= 0) return;
+    const int q0 = qe - len;
+    const int span = r_right < r_left ? len : (r_right - r_left < len ? r_right - r_left : len);
+    const int rmax = span < r_right ? span : r_right;
+    FwdStream L{&pv, q0, r_left};
+    BwdStream R{&pv, qe, r_right};
+    typename W::template Lanes<uint32_t> el, er;
+    LZ_EACH(w, ln)
+    {
+        const int p0 = 32 * ln;
+        const int nl = span - p0, nr = rmax - p0;
+        el[ln] = nl <= 0 ? 0u : (~L.word(ln) & low_mask32(nl > 32 ? 32 : nl));
+        er[ln] = nr <= 0 ? 0u : (~R.word(ln) & low_mask32(nr > 32 ? 32 : nr));
+    }
+    // best split: left[s] + right[span - s], right[u] = 0 for u > rmax (the reference zero-pads)
+    int best = 0, split = 0;
+    {
+        int right_total = 0;
+        for (int t = 0; t < rmax; ++t) right_total += (int)((w.get(er, t >> 5) >> (t & 31)) & 1u);
+        int left = 0, right = right_total;      // right = equal columns among the first (span - s) of R
+        int ru = span;                          // = span - s
+        for (int sp = 0; sp <= span; ++sp) {
+            const int rv = ru > rmax ? 0 : right;
+            if (left + rv >= best) { best = left + rv; split = sp; }
+            if (sp < span) {
+                left += (int)((w.get(el, sp >> 5) >> (sp & 31)) & 1u);
+                // moving to span - (sp+1): drop R column (ru - 1) when it lies inside rmax
+                if (ru - 1 < rmax) right -= (int)((w.get(er, (ru - 1) >> 5) >> ((ru - 1) & 31)) & 1u);
+                --ru;
+            }
+        }
+    }
+    // emit: a pending match factor (q, r, n) is flushed when a column of the other kind follows
+    int fq = 0, fr = 0, fn = 0;          // pending match factor, fn == 0: none
+    int last_flag = -1;                  // flag of the last factor of this gap: 1 match, 0 literals, -1 none
+    int qp = q0;
+    for (int sp = 1; sp <= split; ++sp, ++qp) {
+        const int same = (int)((w.get(el, (sp - 1) >> 5) >> ((sp - 1) & 31)) & 1u);
+        if (same) {
+            if (last_flag == 1) ++fn;
+            else { fq = qp; fr = r_left + sp - 1; fn = 1; }
+        } else {
+            if (fn) { rt.close(fq, fr, fn); fn = 0; }
+            rt.lit(1);
+        }
+        last_flag = same;
+    }
+    if (span < len) {                    // unscanned middle
+        if (fn) { rt.close(fq, fr, fn); fn = 0; }
+        rt.lit(len - span);
+        last_flag = 0;
+    }
+    if (split < span) {
+        const int shift = len - span;
+        const int from_right = span - split;
+        int same = (int)((w.get(er, (from_right - 1) >> 5) >> ((from_right - 1) & 31)) & 1u);
+        qp = q0 + split + shift;
+        if (!same && (split > 0 || shift > 0) && last_flag == 0) rt.lit(1);      // merged: qp NOT advanced
+        else {
+            if (fn) { rt.close(fq, fr, fn); fn = 0; }
+            if (same) { fq = qp; fr = r_right - from_right; fn = 1; }
+            else rt.lit(1);
+            last_flag = same;
+            ++qp;
+        }
+        for (int t = from_right - 1; t > 0; --t, ++qp) {
+            same = (int)((w.get(er, (t - 1) >> 5) >> ((t - 1) & 31)) & 1u);
+            if (same) {
+                if (last_flag == 1) ++fn;
+                else { fq = qp; fr = r_right - t; fn = 1; }
+            } else {
+                if (fn) { rt.close(fq, fr, fn); fn = 0; }
+                rt.lit(1);
+            }
+            last_flag = same;
+        }
+    }
+    if (fn) rt.close(fq, fr, fn);
 }
 
 // ---- anchor lookup: the probe chain of ht_long (parser.cpp:516-530 / :587-601).  Returns the
@@ -626,8 +764,8 @@ struct ParseState {
 
 // One match found at query position qi (parser.cpp:626-698), counts only.  (w2, w3) is the
 // speculative record of hit_probe()/hit_extend() when the match IS that anchor, else w2 == 0.
-template <class W, class PT>
-LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int qi, int lit_k, int pred_k,
+template <class W, class PT, class RS>
+LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, RS& rt, int qi, int lit_k, int pred_k,
                       int best_pos, int best_len, uint32_t w2, uint32_t w3)
 {
     int dist = best_pos - pred_k;
@@ -637,6 +775,10 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int 
         const int g = both_ways_best(w, pv, qi, pred_k - lit_k, best_pos + best_len, lit_k);
         s.curM += g + best_len;
         s.curX += lit_k - g;
+        if (RS::kActive) {
+            both_ways_regions(w, pv, rt, qi, pred_k - lit_k, best_pos + best_len, lit_k);
+            rt.close(qi, best_pos, best_len);
+        }
     } else {
         // distant match: judge the region built so far (:643, eval_region :446-449) ...
         if (s.rs >= 0 && s.re - s.rs >= P.reg) {
@@ -644,7 +786,8 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int 
             s.totX += s.curX;
             ++s.totN;
             s.kept_end = s.re;
-        }
+            if (RS::kActive) rt.end_region(P.reg);
+        } else if (RS::kActive) rt.drop();
         // ... everything since the last kept region is now one literal run (:645-655), which the
         // new match may reclaim backwards (:659-672)
         const int run = qi - s.kept_end;
@@ -664,6 +807,14 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int 
         s.curM = bm + best_len;
         s.curX = back - bm;
         s.rs = qi - back;
+        if (RS::kActive) {
+            if (back > 0) {
+                // the reclaimed columns: first run a distant match, the rest and the match itself close (:664-672)
+                const FwdStream bw{&pv, qi - back, best_pos - back};
+                rt.range(qi - back, best_pos - back, back, summarize_range(w, bw, back), true);
+                rt.close(qi, best_pos, best_len);
+            } else rt.dist(qi, best_pos, best_len);
+        }
     }
     const int qn = qi + best_len;
     const int pn = best_pos + best_len;
@@ -679,6 +830,10 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, int 
     }
     s.curM += fm;
     s.curX += fwd - fm;
+    if (RS::kActive && fwd > 0) {
+        const FwdStream fs{&pv, qn, pn};
+        rt.range(qn, pn, fwd, summarize_range(w, fs, fwd), false);
+    }
     s.i = qn + fwd;
     s.pred = pn + fwd;
     s.lit = 0;
@@ -815,10 +970,11 @@ LZ_HD Event next_event(W& w, const LI& r_p, const LU& r_pos, const LU& r_w2, con
 //          from hit to hit; with one (the mqd positions after a match) it also looks for seeds
 //          along the diagonals of the prediction window.
 // `list` is 32 uint16 of per-warp scratch (shared memory on the device).
-template <class W, class PT>
-LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc)
+template <class W, class PT, class RS>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc, RS& rt)
 {
     uint16_t* list = sc->list;
+    if (RS::kActive) rt.clear_all();
     ParseState s;
     s.i = 0; s.pred = -1; s.lit = 0;
     s.rs = -1; s.re = 0; s.kept_end = 0;
@@ -942,12 +1098,13 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 r_pos[ln] = a; r_w2[ln] = b | ((uint32_t)r_run[ln] << HIT_RUN_SHIFT); r_w3[ln] = 0;
             }
             w.sync();
+            if (!RS::kActive)       // the regions kernel needs the columns, not their counts: no records
             LZ_EACH(w, ln)
             {
                 if ((r_w2[ln] & (HIT_LIVE | HIT_DEFER)) == HIT_LIVE) hit_extend(pv, P, r_p[ln], (int)r_pos[ln], r_w2[ln], r_w3[ln]);
             }
             w.sync();
-            if (PT::kSpecSeeds && P.mqd <= SPEC_MAX_K) {
+            if (PT::kSpecSeeds && !RS::kActive && P.mqd <= SPEC_MAX_K) {
                 LZ_EACH(w, ln)
                 {
                     if (r_w2[ln] & HIT_FWD) {
@@ -977,7 +1134,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         //   * nothing at all for mqd+1 positions: the prediction expires.
         // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
         // general code below, which re-derives the same step.
-        if (PT::kSpecSeeds && (s.pred < 0 || (s.lit == 0 && i0 == spec_i0 && spec_K1 > 0))) {
+        if (PT::kSpecSeeds && !RS::kActive && (s.pred < 0 || (s.lit == 0 && i0 == spec_i0 && spec_K1 > 0))) {
             const Event ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
             const int qi = ev.qi;
             const int ka = qi - i0;
@@ -1159,7 +1316,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         }
         }
         if (matched) {
-            take_match(w, pv, P, s, m_qi, m_lit, m_pred, m_pos, m_len, m_w2, m_w3);
+            take_match(w, pv, P, s, rt, m_qi, m_lit, m_pred, m_pos, m_len, m_w2, m_w3);
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
             lz_matches++;
 #endif
@@ -1196,7 +1353,9 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         }
         s.curM += mt;
         s.curX += last - mt;
+        if (RS::kActive) rt.range(s.i - s.lit, s.pred - s.lit - P.msl, n, summarize_range(w, ts, n), false);
     }
+    if (RS::kActive) rt.end_region(P.reg);      // the last region is never dropped by the parse
     if (s.rs >= 0 && s.curM + s.curX >= P.reg) {
         s.totM += s.curM;
         s.totX += s.curX;
@@ -1205,6 +1364,14 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     PairResult r;
     r.m = s.totM; r.x = s.totX; r.n = s.totN;
     return r;
+}
+
+// the counting kernel: no region records
+template <class W, class PT>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc)
+{
+    NoRegions none;
+    return parse_pair(w, pv, P, sc, none);
 }
 
 }  // namespace lzani

@@ -4,6 +4,7 @@
 // This is not a CPU fallback: it is built only by tests/emul/Makefile into
 // tests/emul/liblzani_emul.so, is never linked into liblzani_b200.so and is ~100x slower than
 // the reference.  The library itself fails loudly without a CUDA device.
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstring>
@@ -123,8 +124,47 @@ extern "C" void lzani_emul_spec_stats(long* used, long* mismatches)
     *mismatches = lz_spec_mismatches;
 }
 
-extern "C" int lzani_emul_regions(const int32_t*, const uint8_t*, uint32_t, const uint8_t*, uint32_t, int32_t*,
-                                  uint32_t, int32_t*)
+namespace {
+struct VecOut {
+    std::vector<RegionRec> v;
+    void emit(const RegionRec& g) { v.push_back(g); }
+};
+}  // namespace
+
+// regions of one pair through the kernel source's region fold (regions.h), sorted the way
+// calc_regions sorts them (length descending, then seq_start)
+extern "C" int lzani_emul_regions(const int32_t* p8, const uint8_t* ref3, uint32_t ref_len, const uint8_t* qry3,
+                                  uint32_t qry_len, int32_t* out6, uint32_t cap, int32_t* stats3)
 {
-    return -1;   // regions are not emulated
+    Prm P{p8[0], p8[1], p8[2], p8[3], p8[4], p8[5], p8[6], p8[7]};
+    HostSeq r, q;
+    build_seq(r, ref3, ref_len, P);
+    build_seq(q, qry3, qry_len, P);
+    HostIndex ix;
+    build_index(ix, r, P);
+    PairView pv;
+    pv.q = q.q.data(); pv.Dq = q.len + P.mrd;
+    pv.r = r.r.data(); pv.Dr = r_form_len(r.len, P.mrd);
+    pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
+    pv.table = ix.table.data(); pv.tbits = ix.tbits;
+    HostWarp w;
+    WarpScratch scratch;
+    VecOut out;
+    RegionTracker<VecOut> rt;
+    rt.out = &out;
+    PairResult res;
+    if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch, rt); }
+    else res = parse_pair(w, pv, P, &scratch, rt);
+    if (stats3) { stats3[0] = res.m; stats3[1] = res.x; stats3[2] = res.n; }
+    std::stable_sort(out.v.begin(), out.v.end(), [](const RegionRec& a, const RegionRec& b) {
+        const int la = a.seq_end - a.seq_start, lb = b.seq_end - b.seq_start;
+        if (la != lb) return la > lb;
+        return a.seq_start < b.seq_start;
+    });
+    for (size_t i = 0; i < out.v.size() && i < cap; ++i) {
+        const RegionRec& g = out.v[i];
+        int32_t* o = out6 + 6 * i;
+        o[0] = g.ref_start; o[1] = g.ref_end; o[2] = g.seq_start; o[3] = g.seq_end; o[4] = g.num_matches; o[5] = g.num_mismatches;
+    }
+    return (int)out.v.size();
 }

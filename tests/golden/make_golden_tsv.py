@@ -44,6 +44,17 @@ def main():
         with gzip.GzipFile(os.path.join(HERE, name + ".ani.ids.tsv.gz"), "wb", mtime=0) as f:
             f.write(ids)
         print(name, len(data), hashlib.md5(data).hexdigest())
+    # --out-alignment (line order depends on thread interleaving in the reference: compare sorted)
+    out = os.path.join(tmp, "aln_main.tsv")
+    aln = os.path.join(tmp, "aln.tsv")
+    subprocess.run([CLI, "all2all", "--in-fasta", os.path.join(REF, "example/multifasta.fna"), "--out", out,
+                    "--out-alignment", aln, "-V", "1"], check=True, stderr=subprocess.DEVNULL)
+    lines = sorted(open(aln, "rb").read().splitlines(keepends=True))
+    want = sorted(open(os.path.join(REF, "example/output/ani.aln.tsv"), "rb").read().splitlines(keepends=True))
+    assert lines == want, "reference CLI alignment output differs from the reference's own golden"
+    with gzip.GzipFile(os.path.join(HERE, "example_default.aln.sorted.tsv.gz"), "wb", mtime=0) as f:
+        f.write(b"".join(lines))
+    print("example alignment", len(lines), "lines")
     shutil.copy(os.path.join(REF, "example", "fltr.txt"), os.path.join(HERE, "example_fltr.txt"))
     shutil.rmtree(tmp)
 

@@ -69,3 +69,23 @@ def test_kernel_source_randomized_differential(emul, seed):
     names = list(names) + ["rep"]
     ss = hostio.SeqSet(names, seqs)
     assert np.array_equal(emul.run_rows(ss, None, threads=4), Oracle().run_rows(ss, None, threads=4))
+
+
+@pytest.mark.parametrize("sname,params", [("example", None), ("example", mg.ODD), ("edge", None), ("synth_small", mg.LONGP)])
+def test_region_fold_matches_oracle_regions(emul, sname, params):
+    """--out-alignment path: the streaming region fold of the kernel source (regions.h) against the
+    oracle's calc_regions over its factor vector, every ordered pair of the set."""
+    ss = mg.get_set(sname)
+    orc = Oracle()
+    n = len(ss)
+    total = 0
+    for r in range(n):
+        for q in range(n):
+            if r == q:
+                continue
+            a, sa = emul.regions(ss, params, r, q)
+            b, sb = orc.regions(ss, params, r, q)
+            assert np.array_equal(sa, sb), (r, q)
+            assert a.shape == b.shape and np.array_equal(a, b), (r, q)
+            total += len(b)
+    assert total > 0

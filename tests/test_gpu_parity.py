@@ -166,3 +166,33 @@ def test_megabase_genomes_config5(params):
     got, _ = run_gpu(ss, params)
     want = Oracle().run_rows(ss, params)
     assert np.array_equal(got, want), f"{got.tolist()} vs {want.tolist()}"
+
+
+@pytest.mark.parametrize("sname,params", [("example", None), ("example", mg.ODD), ("synth_small", mg.LONGP)])
+def test_region_records_match_oracle(sname, params):
+    """--out-alignment path (lzani_run_rows_regions, replaces CParser::get_parsing): counts and region
+    records of every ordered pair against the oracle; a too small buffer is reported with the needed
+    size and nothing written."""
+    ss = mg.get_set(sname)
+    n = len(ss)
+    orc = Oracle()
+    m = lz.Matcher(params=params, device=0)
+    try:
+        m.set_sequences(ss)
+        out, off, regs = m.run_rows_regions(np.arange(n, dtype=np.uint32), cap=8)     # forces the retry path
+        assert np.array_equal(out, m.all2all())
+        k = 0
+        total = 0
+        for r in range(n):
+            for q in range(n):
+                if q == r:
+                    continue
+                want, st = orc.regions(ss, params, r, q)
+                got = regs[int(off[k]):int(off[k + 1])]
+                assert got.shape == want.shape and np.array_equal(got, want), (r, q)
+                assert out[k].tolist() == st.tolist()
+                total += len(want)
+                k += 1
+        assert total == len(regs) and total > 0
+    finally:
+        m.close()

@@ -85,3 +85,22 @@ def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     want_tsv, want_ids = golden(case)
     assert open(out, "rb").read() == want_tsv
     assert open(str(out).replace("ani.tsv", "ani.ids.tsv"), "rb").read() == want_ids
+
+
+@pytest.mark.gpu
+def test_cli_out_alignment_identical_to_reference(tmp_path):
+    """--out-alignment: region records from the B200 regions kernel written by the reference's own
+    store_alignment; the reference's line order depends on thread interleaving, so sorted lines are
+    compared."""
+    need_cli()
+    ss = mg.get_set("example")
+    fa = tmp_path / "in.fna"
+    write_fasta(fa, ss)
+    out, aln = tmp_path / "ani.tsv", tmp_path / "ani.aln.tsv"
+    r = subprocess.run([CLI, "all2all", "--in-fasta", str(fa), "--out", str(out), "--out-alignment", str(aln), "-V", "1"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = gzip.open(os.path.join(GOLD, "example_default.aln.sorted.tsv.gz")).read().splitlines(keepends=True)
+    got = sorted(open(aln, "rb").read().splitlines(keepends=True))
+    assert got == want
+    assert open(out, "rb").read() == golden("example_default")[0]
