@@ -316,7 +316,7 @@ def main():
                 "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                 "config": {"workload": f"synthetic viral all2all, {n} genomes ~50 kb in mutated families of 20 (seed {synth.SEED}), default params, {int(total_pairs)} ordered pairs per step, pair list sharded by reference row over {world} GPU(s)",
                            "genomes": n, "params": hostio.DEFAULT_PARAMS, "pairs_per_step": int(total_pairs),
-                           "l2_policy": "inputs larger than L2: per step the kernels touch sequence records + indices of all references (~%.1f GB)" % ((m.timing()["r_bases"] * 26 + total_len * 0.5) / 1e9)},
+                           "l2_policy": "inputs larger than L2: per step the kernels touch sequence records + indices of all references (~%.1f GB)" % ((r_bases * 26 + total_len * 1.0) / 1e9)},
                 "query_gbp_per_sec": total_qbases / (dev_ms_step / 1e3) / 1e9,
                 "wall_ms_per_step": wall_ms_step, "parse_kernel_ms_per_step": parse_ms_step,
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
