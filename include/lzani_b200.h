@@ -10,8 +10,9 @@
  *     parser.prepare_data(seq_view(qry), ..)         |  lzani_set_sequences() once, then
  *     parser.parse()                                 |-> lzani_run() / lzani_run_rows()
  *     results_t r = parser.calc_stats()             /     (batch form: one call, all pairs)
- *     vector<region_t> v = parser.get_parsing()     -> not yet covered (--out-alignment only;
- *                                                       SURVEY 8f-2, a "next" row)
+ *     vector<region_t> v = parser.get_parsing()     -> lzani_run_rows_regions() (--out-alignment)
+ * and, past the parse, the pairing + --out-filter arithmetic of store_results
+ * (lz_matcher.cpp:404-463)                          -> lzani_filter_pairs()
  *
  * Plain pointers and sizes only; no C++/torch types.  All work is done by hand-written
  * sm_100a CUDA kernels; there is NO CPU fallback: every entry point fails with
@@ -59,6 +60,22 @@ typedef struct lzani_region_t {
     int32_t num_matches, num_mismatches;
 } lzani_region_t;
 
+/* Thresholds of --out-filter (params.h:98-99, set_output_filter :200-209) in the order the
+ * reference tests them (lz_matcher.cpp:451-462); 0 = not set. */
+typedef struct lzani_out_filter_t {
+    double gani, ani, tani, qcov, rcov;
+} lzani_out_filter_t;
+
+/* One unordered pair (a < b) that survives the filter: both directions' results_t, as
+ * store_results pairs them up (lz_matcher.cpp:404-418).  ab = parse of b against the index of a
+ * (`q->results`), ba = parse of a against the index of b (`p->results`).  lines bit 0: the output
+ * line "reference a, query b" passes, bit 1: the line "reference b, query a" passes. */
+typedef struct lzani_pair_t {
+    uint32_t a, b;
+    lzani_result_t ab, ba;
+    uint32_t lines;
+} lzani_pair_t;
+
 /* Device timings of the last lzani_run*() call (CUDA events on the library's stream). */
 typedef struct lzani_timing_t {
     double h2d_ms;      /* pair list (+ sequences if not yet resident) host->device */
@@ -74,6 +91,8 @@ typedef struct lzani_timing_t {
     uint64_t d2h_bytes; /* bytes copied device->host inside the call              */
     uint32_t launches;  /* kernels launched inside the call                       */
     uint32_t n_batches; /* reference batches the index memory budget forced       */
+    double filter_ms;   /* lzani_filter_pairs: tables H2D, F1-F3, surviving pairs D2H */
+    uint64_t filter_d2h_bytes; /* bytes lzani_filter_pairs copied device->host    */
 } lzani_timing_t;
 
 enum {
@@ -130,6 +149,23 @@ int lzani_run_rows_regions(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_
 int lzani_run_rows_resident(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref_ids,
                             const uint64_t* row_off, const uint32_t* q_ids, int repeat,
                             lzani_result_t* out);
+
+/* Replaces the pairing, derived-metric and --out-filter arithmetic of store_results
+ * (lz_matcher.cpp:404-463) as a device-side pre-filter.  Call after
+ * lzani_run_rows_resident(ctx, ..., repeat 1, out NULL) -- or any lzani_run_rows* -- whose results are
+ * still on the device.  For every ordered pair (a, b), a < b, of ctx's rows the kernel finds the
+ * opposite direction (row b, entry a), computes gani/ani/tani/qcov/rcov of both output lines in IEEE
+ * double exactly as the reference does, and keeps the pair when at least one line passes.  Only the
+ * surviving pairs are copied to pairs[] (CSR order of ctx's rows; *n_out = their number; when it
+ * exceeds cap nothing is written and LZANI_ERR_NOMEM is returned).
+ * group / n_group: all contexts of this process whose rows together hold both directions (one per
+ * GPU, ctx included; NULL = ctx alone).  Rows owned by other GPUs are read in place over NVLink peer
+ * access -- no host round trip, no collective; none of the group's contexts may start a new run until
+ * every lzani_filter_pairs call of the group has returned.  eff_len[i] = length of sequence i without
+ * its contig separators (`len - (no_parts-1)*mrd`, lz_matcher.cpp:437).  Query ids must ascend within
+ * every CSR row; a missing opposite direction is an error (the reference asserts, :417). */
+int lzani_filter_pairs(lzani_ctx* ctx, lzani_ctx* const* group, int n_group, const uint32_t* eff_len,
+                       const lzani_out_filter_t* flt, lzani_pair_t* pairs, uint64_t cap, uint64_t* n_out);
 
 int lzani_get_timing(const lzani_ctx* ctx, lzani_timing_t* t);
 

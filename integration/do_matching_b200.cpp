@@ -9,12 +9,20 @@
 // the filter rows), and `results[r]` is filled with id-sorted id_results_t exactly as the
 // reference leaves it for store_results (lz_matcher.cpp:252-255, :404-418).
 //
+// With --out-filter (two-TSV output, no --out-alignment) the results stay on the GPUs: after the parse
+// every GPU pairs up the two directions of its unordered pairs -- reading the rows owned by the other
+// GPUs in place over NVLink peer access -- evaluates the reference's filter arithmetic
+// (lz_matcher.cpp:434-463) and ships only the surviving pairs (lzani_filter_pairs).
+// `results` then holds just those pairs; the unmodified store_results re-tests and formats them, so
+// the text is identical while the D2H volume and the host-side result table shrink to the survivors.
+//
 // Everything else of the reference (CLI, params, loaders, filter, reorder, TSV writers) is compiled
 // UNMODIFIED from /root/reference/src by integration/Makefile; this file is the only host source of
 // ours in the binary.  There is no CPU fallback: without a B200 the program prints the library's
 // error and exits 1 (the reference's own error convention, lz_matcher.h:61-65).
 #include <algorithm>
 #include <atomic>
+#include <barrier>
 #include <cstdlib>
 #include <iostream>
 #include <string>
@@ -92,6 +100,26 @@ void CLZMatcher::do_matching()
     // lz_matcher.cpp:226-227): smaller submits keep that buffer bounded.
     const uint64_t max_pairs_per_call = f_alignment ? (1ull << 20) : (16ull << 20);
 
+    // ---- device-side --out-filter (see the header comment)
+    const bool device_filter = params.output_filter_mask != 0 && params.output_type == output_type_t::two_tsv &&
+                               !f_alignment && !getenv("LZANI_HOST_FILTER");
+    lzani_out_filter_t flt{};
+    std::vector<uint32_t> eff_len(n);
+    if (device_filter) {
+        flt.gani = params.output_filter_vals[(uint32_t)output_component_t::gani];
+        flt.ani = params.output_filter_vals[(uint32_t)output_component_t::ani];
+        flt.tani = params.output_filter_vals[(uint32_t)output_component_t::tani];
+        flt.qcov = params.output_filter_vals[(uint32_t)output_component_t::qcov];
+        flt.rcov = params.output_filter_vals[(uint32_t)output_component_t::rcov];
+        for (uint32_t i = 0; i < n; ++i) {
+            auto it = seq_reservoir.get_sequence(i);
+            eff_len[i] = it->len - (it->no_parts - 1) * (uint32_t)params.max_dist_in_ref;   // lz_matcher.cpp:437
+        }
+    }
+    std::vector<lzani_ctx*> group(G, nullptr);
+    std::vector<std::vector<lzani_pair_t>> survivors(G);
+    std::barrier sync_point((std::ptrdiff_t)G);
+
     std::atomic<uint64_t> done_rows{0};
     std::vector<std::thread> workers;
     for (uint32_t g = 0; g < G; ++g) {
@@ -100,6 +128,41 @@ void CLZMatcher::do_matching()
             const int dev = devs[g];
             if (lzani_create(&ctx, &P, &dev, 1) != LZANI_OK) die("lzani_create", ctx);
             if (lzani_set_sequences(ctx, n, data.data(), len.data()) != LZANI_OK) die("lzani_set_sequences", ctx);
+
+            if (device_filter) {
+                // one submit with all rows of this GPU; the results stay in its HBM
+                std::vector<uint32_t> rows, q_ids;
+                std::vector<uint64_t> row_off(1, 0);
+                for (uint32_t r = g; r < n; r += G) {
+                    rows.push_back(r);
+                    if (dense) row_off.push_back(row_off.back() + (n - 1));
+                    else {
+                        const size_t a = q_ids.size();
+                        for (auto id : filter.get_row(r)) q_ids.push_back((uint32_t)id);
+                        std::sort(q_ids.begin() + a, q_ids.end());
+                        row_off.push_back(q_ids.size());
+                        filter.clear_row(r);
+                    }
+                }
+                if (lzani_run_rows_resident(ctx, (uint32_t)rows.size(), rows.data(), dense ? nullptr : row_off.data(),
+                                            dense ? nullptr : q_ids.data(), 1, nullptr) != LZANI_OK)
+                    die("lzani_run_rows_resident", ctx);
+                group[g] = ctx;
+                sync_point.arrive_and_wait();               // every GPU's rows are complete
+                std::vector<lzani_pair_t>& sv = survivors[g];
+                sv.resize(1024);
+                for (;;) {
+                    uint64_t need = 0;
+                    const int rc = lzani_filter_pairs(ctx, group.data(), (int)G, eff_len.data(), &flt, sv.data(), sv.size(), &need);
+                    if (rc == LZANI_ERR_NOMEM && need > sv.size()) { sv.resize(need); continue; }
+                    if (rc != LZANI_OK) die("lzani_filter_pairs", ctx);
+                    sv.resize(need);
+                    break;
+                }
+                sync_point.arrive_and_wait();               // nobody reads a peer's rows any more
+                lzani_destroy(ctx);
+                return;
+            }
 
             std::vector<uint32_t> rows, q_ids;
             std::vector<uint64_t> row_off;
@@ -170,6 +233,16 @@ void CLZMatcher::do_matching()
         });
     }
     for (auto& t : workers) t.join();
+    if (device_filter) {
+        // only the surviving pairs reach the host: both directions go into `results`, id-sorted, as
+        // store_results expects them (lz_matcher.cpp:404-418)
+        for (const auto& sv : survivors)
+            for (const lzani_pair_t& p : sv) {
+                results[p.a].emplace_back(p.b, results_t(p.ab.sym_in_matches, p.ab.sym_in_literals, p.ab.no_components));
+                results[p.b].emplace_back(p.a, results_t(p.ba.sym_in_matches, p.ba.sym_in_literals, p.ba.no_components));
+            }
+        for (auto& row : results) std::sort(row.begin(), row.end());
+    }
     if (params.verbosity_level >= 2)
         cerr << endl;
 }

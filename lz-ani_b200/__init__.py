@@ -34,8 +34,8 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "capi.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "regions.h", "simt.h")] + [
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "capi.cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "regions.h", "simt.h", "outfilter.h")] + [
         os.path.join(ROOT, "include", "lzani_b200.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
@@ -49,7 +49,8 @@ class TimingStruct(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("pack_ms", C.c_double), ("index_ms", C.c_double), ("parse_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("n_pairs", C.c_uint64), ("q_bases", C.c_uint64),
                 ("r_bases", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("launches", C.c_uint32), ("n_batches", C.c_uint32)]
+                ("launches", C.c_uint32), ("n_batches", C.c_uint32),
+                ("filter_ms", C.c_double), ("filter_d2h_bytes", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -79,6 +80,7 @@ def load_library() -> C.CDLL:
     lib.lzani_run_rows.argtypes = [vp, u32, vp, vp, vp, vp]
     lib.lzani_run_rows_resident.argtypes = [vp, u32, vp, vp, vp, C.c_int, vp]
     lib.lzani_run_rows_regions.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, u64, vp]
+    lib.lzani_filter_pairs.argtypes = [vp, vp, C.c_int, vp, vp, vp, u64, vp]
     lib.lzani_get_timing.argtypes = [vp, C.POINTER(TimingStruct)]
     lib.lzani_set_index_budget.argtypes = [vp, u64]
     lib.lzani_last_error.argtypes = [vp]
@@ -206,5 +208,37 @@ def _run_rows_regions(self, rows, row_off=None, q_ids=None, cap: int = 1 << 16):
 
 
 Matcher.run_rows_regions = _run_rows_regions
+
+PAIR_DTYPE = np.dtype([("a", np.uint32), ("b", np.uint32), ("ab", np.int32, 3), ("ba", np.int32, 3), ("lines", np.uint32)])
+FILTER_KEYS = ("gani", "ani", "tani", "qcov", "rcov")
+
+
+def _filter_pairs(self, eff_len, flt: dict, group=None, cap: int = 1 << 12):
+    """Device-side pairing + derived metrics + --out-filter compaction (lzani_filter_pairs;
+    replaces the arithmetic of store_results, lz_matcher.cpp:404-463) over the results the last
+    run_rows(..., resident_repeat=1) left on the device.  flt: thresholds by name (missing = 0).
+    group: the Matchers (one per GPU) that together hold both directions; None = this one.
+    Returns a structured array (PAIR_DTYPE) of the surviving unordered pairs in CSR order."""
+    eff_len = np.ascontiguousarray(eff_len, dtype=np.uint32)
+    assert eff_len.size == self.n
+    thr = np.array([float(flt.get(k, 0.0)) for k in FILTER_KEYS], dtype=np.float64)
+    grp_p, n_grp = None, 0
+    if group:
+        grp_p = (C.c_void_p * len(group))(*[g.h for g in group])
+        n_grp = len(group)
+    for _ in range(2):
+        pairs = np.zeros(max(cap, 1), dtype=PAIR_DTYPE)
+        n_out = C.c_uint64(0)
+        rc = self.lib.lzani_filter_pairs(self.h, grp_p, n_grp, eff_len.ctypes.data, thr.ctypes.data,
+                                         pairs.ctypes.data, cap, C.byref(n_out))
+        if rc == 4 and n_out.value > cap:
+            cap = int(n_out.value)
+            continue
+        self._check(rc, "lzani_filter_pairs")
+        return pairs[: int(n_out.value)].copy()
+    raise LzaniError("lzani_filter_pairs: survivor count changed between calls")
+
+
+Matcher.filter_pairs = _filter_pairs
 
 from .sharding import shard_rows  # noqa: E402,F401

@@ -50,6 +50,19 @@ struct lzani_ctx {
     DevRegion* d_regs = nullptr; uint64_t regs_cap = 0;     // regions kernel (--out-alignment)
     unsigned long long* d_reg_counter = nullptr;
 
+    // the last run, kept for lzani_filter_pairs (results stay in d_out until the next run)
+    std::vector<uint32_t> last_row_ref;
+    std::vector<uint64_t> last_row_off;
+    bool last_valid = false, last_sparse = false, last_sorted = true;
+
+    // out-filter compaction (postproc.cu)
+    uint8_t* d_flags = nullptr; uint64_t flags_cap = 0;
+    uint32_t* d_blk_cnt = nullptr; uint64_t blk_cnt_cap = 0;
+    unsigned long long* d_blk_off = nullptr; uint64_t blk_off_cap = 0;
+    RowLoc* d_loc = nullptr; uint64_t loc_cap = 0;
+    uint32_t* d_eff_len = nullptr; uint64_t eff_cap = 0;
+    PairOut* d_pairs = nullptr; uint64_t pairs_cap = 0;
+
     cudaEvent_t ev[8]{};
     lzani_timing_t timing{};
 };
@@ -87,6 +100,7 @@ void free_sequences(lzani_ctx* c)
     cudaFree(c->d_rec_base); c->d_rec_base = nullptr;
     cudaFree(c->d_recs); c->d_recs = nullptr;
     c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
+    c->last_valid = false;
 }
 
 float ms_between(cudaEvent_t a, cudaEvent_t b)
@@ -153,6 +167,8 @@ extern "C" void lzani_destroy(lzani_ctx* c)
         cudaFree(c->d_row_ref); cudaFree(c->d_row_idx); cudaFree(c->d_row_off); cudaFree(c->d_blk_base);
         cudaFree(c->d_q_ids); cudaFree(c->d_out); cudaFree(c->d_counter);
         cudaFree(c->d_regs); cudaFree(c->d_reg_counter);
+        cudaFree(c->d_flags); cudaFree(c->d_blk_cnt); cudaFree(c->d_blk_off); cudaFree(c->d_loc);
+        cudaFree(c->d_eff_len); cudaFree(c->d_pairs);
         for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
         if (c->stream) cudaStreamDestroy(c->stream);
     }
@@ -289,11 +305,17 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
     }
     const uint64_t n_pairs = row_off[n_rows];
     const uint32_t* q_src = q_ids ? q_ids + row_off_in[0] : nullptr;
-    if (q_ids)
+    c->last_valid = false;
+    bool rows_sorted = true;
+    if (q_ids) {
         for (uint64_t k = 0; k < n_pairs; ++k) {
             if (q_src[k] >= n) return fail(c, LZANI_ERR_ARG, "query id out of range");
             q_bases += c->meta[q_src[k]].len;
         }
+        for (uint32_t j = 0; j < n_rows && rows_sorted; ++j)
+            for (uint64_t k = row_off[j] + 1; k < row_off[j + 1]; ++k)
+                if (q_src[k] <= q_src[k - 1]) { rows_sorted = false; break; }
+    }
     std::vector<RowPlan> plan(n_rows);
     for (uint32_t j = 0; j < n_rows; ++j) {
         RowPlan& rp = plan[j];
@@ -437,6 +459,11 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
     T.q_bases = q_bases * (uint64_t)repeat;
     T.r_bases = r_bases * (uint64_t)repeat;
     c->timing = T;
+    c->last_row_ref = row_ref;
+    c->last_row_off = row_off;
+    c->last_sparse = q_ids != nullptr;
+    c->last_sorted = rows_sorted;
+    c->last_valid = true;
     if (rq) {
         // regions: bring them back, group by pair (counting sort), order each group like calc_regions
         unsigned long long total = 0;
@@ -495,4 +522,84 @@ extern "C" int lzani_run_rows_resident(lzani_ctx* c, uint32_t n_rows, const uint
                                        lzani_result_t* out)
 {
     return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, repeat, out, false);
+}
+
+// ------------------------------------------------------------------------------------------
+// derived metrics + --out-filter compaction on the device.
+extern "C" int lzani_filter_pairs(lzani_ctx* c, lzani_ctx* const* group, int n_group, const uint32_t* eff_len,
+                                  const lzani_out_filter_t* flt, lzani_pair_t* pairs, uint64_t cap, uint64_t* n_out)
+{
+    static_assert(sizeof(lzani_pair_t) == sizeof(PairOut), "lzani_pair_t layout");
+    if (!c) return LZANI_ERR_ARG;
+    if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
+    if (!eff_len || !flt || !n_out || (cap && !pairs)) return fail(c, LZANI_ERR_ARG, "eff_len / flt / pairs / n_out == NULL");
+    if (!c->last_valid) return fail(c, LZANI_ERR_STATE, "no results on the device: run lzani_run_rows* first");
+    lzani_ctx* self[1] = {c};
+    if (!group || n_group < 1) { group = self; n_group = 1; }
+    const uint32_t n = c->n_seqs;
+    LZ_CUDA(c, cudaSetDevice(c->device));
+
+    // where every reference row's results live, across the group
+    std::vector<RowLoc> loc(n ? n : 1, RowLoc{nullptr, nullptr, 0, 0});
+    for (int g = 0; g < n_group; ++g) {
+        const lzani_ctx* m = group[g];
+        if (!m || !m->last_valid) return fail(c, LZANI_ERR_STATE, "a context of the group holds no results");
+        if (m->n_seqs != n) return fail(c, LZANI_ERR_ARG, "the contexts of the group hold different sequence sets");
+        if (m->last_sparse && !m->last_sorted)
+            return fail(c, LZANI_ERR_ARG, "query ids must ascend within every row for lzani_filter_pairs");
+        if (m->device != c->device) {
+            int can = 0;
+            LZ_CUDA(c, cudaDeviceCanAccessPeer(&can, c->device, m->device));
+            if (!can) return fail(c, LZANI_ERR_CUDA, "no peer access from device " + std::to_string(c->device) + " to " + std::to_string(m->device));
+            const cudaError_t e = cudaDeviceEnablePeerAccess(m->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+            else if (e != cudaSuccess) return fail(c, LZANI_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+        }
+        for (size_t j = 0; j < m->last_row_ref.size(); ++j) {
+            const uint64_t a = m->last_row_off[j], b = m->last_row_off[j + 1];
+            RowLoc& L = loc[m->last_row_ref[j]];
+            L.res = (const uint8_t*)m->d_out + a * sizeof(lzani_result_t);
+            L.q = m->last_sparse ? m->d_q_ids + a : nullptr;
+            L.cnt = (uint32_t)(b - a);
+        }
+    }
+
+    const uint64_t n_pairs = c->last_row_off.empty() ? 0 : c->last_row_off.back();
+    const uint64_t nb = filter_blocks(n_pairs);
+    if (int rc = ensure(c, c->d_loc, c->loc_cap, (uint64_t)loc.size())) return rc;
+    if (int rc = ensure(c, c->d_eff_len, c->eff_cap, (uint64_t)(n ? n : 1))) return rc;
+    if (int rc = ensure(c, c->d_flags, c->flags_cap, n_pairs)) return rc;
+    if (int rc = ensure(c, c->d_blk_cnt, c->blk_cnt_cap, nb)) return rc;
+    if (int rc = ensure(c, c->d_blk_off, c->blk_off_cap, nb + 1)) return rc;
+
+    cudaStream_t st = c->stream;
+    FilterArgs A;
+    A.row_ref = c->d_row_ref; A.row_off = c->d_row_off; A.q_ids = c->last_sparse ? c->d_q_ids : nullptr; A.res = c->d_out;
+    A.n_rows = (uint32_t)c->last_row_ref.size(); A.n_pairs = n_pairs;
+    A.loc = c->d_loc; A.eff_len = c->d_eff_len;
+    A.flt = OutFilter{flt->gani, flt->ani, flt->tani, flt->qcov, flt->rcov};
+
+    LZ_CUDA(c, cudaEventRecord(c->ev[0], st));
+    LZ_CUDA(c, cudaMemcpyAsync(c->d_loc, loc.data(), sizeof(RowLoc) * loc.size(), cudaMemcpyHostToDevice, st));
+    if (n) LZ_CUDA(c, cudaMemcpyAsync(c->d_eff_len, eff_len, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, st));
+    LZ_CUDA(c, cudaMemsetAsync(c->d_reg_counter, 0, sizeof(unsigned long long), st));
+    LZ_CUDA(c, launch_filter_count(st, A, c->d_flags, c->d_blk_cnt, c->d_blk_off, c->d_reg_counter));
+    unsigned long long total = 0, missing = 0;
+    LZ_CUDA(c, cudaMemcpyAsync(&total, c->d_blk_off + nb, sizeof(total), cudaMemcpyDeviceToHost, st));
+    LZ_CUDA(c, cudaMemcpyAsync(&missing, c->d_reg_counter, sizeof(missing), cudaMemcpyDeviceToHost, st));
+    LZ_CUDA(c, cudaStreamSynchronize(st));
+    *n_out = total;
+    if (missing)
+        return fail(c, LZANI_ERR_ARG, "the pair list is not symmetric: the opposite direction of " + std::to_string(missing) +
+                                          " pairs is missing (the reference asserts it, lz_matcher.cpp:417)");
+    if (total > cap) return fail(c, LZANI_ERR_NOMEM, "pairs buffer too small: " + std::to_string(total) + " pairs survive the filter");
+    if (int rc = ensure(c, c->d_pairs, c->pairs_cap, (uint64_t)total)) return rc;
+    LZ_CUDA(c, launch_filter_emit(st, A, c->d_flags, c->d_blk_off, c->d_pairs, total));
+    if (total) LZ_CUDA(c, cudaMemcpyAsync(pairs, c->d_pairs, sizeof(PairOut) * total, cudaMemcpyDeviceToHost, st));
+    LZ_CUDA(c, cudaEventRecord(c->ev[1], st));
+    LZ_CUDA(c, cudaStreamSynchronize(st));
+    c->timing.filter_ms = ms_between(c->ev[0], c->ev[1]);
+    c->timing.filter_d2h_bytes = sizeof(PairOut) * total + 16;
+    c->timing.launches += nb ? 3 : 1;
+    return LZANI_OK;
 }

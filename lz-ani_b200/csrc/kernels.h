@@ -5,6 +5,7 @@
 
 #include "layout.h"
 #include "regions.h"
+#include "outfilter.h"
 
 #define LZ_PARSE_THREADS 128
 #ifndef LZ_PARSE_MIN_BLOCKS
@@ -37,5 +38,23 @@ cudaError_t launch_parse(cudaStream_t st, int grid_blocks, const Rec* recs, cons
                          uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint64_t pair_end,
                          const Prm& P, const uint32_t* bitmap_pool, const uint64_t* table_pool,
                          unsigned long long* counter, void* out);
+
+// ---- postproc.cu: pairing of the two directions, derived metrics, --out-filter compaction
+// where the results of reference row r live (this GPU or a peer): res[i] is the result of the i-th
+// query of the row, q its ascending query ids (nullptr = dense row: every id != r)
+struct RowLoc { const void* res; const uint32_t* q; uint32_t cnt; uint32_t pad_; };
+struct FilterArgs {
+    const uint32_t* row_ref; const uint64_t* row_off; const uint32_t* q_ids; const void* res;   // this context's last run
+    uint32_t n_rows; uint64_t n_pairs;
+    const RowLoc* loc;            // per sequence id
+    const uint32_t* eff_len;      // per sequence id: length without contig separators
+    OutFilter flt;
+};
+struct PairOut { uint32_t a, b; int32_t ab[3], ba[3]; uint32_t lines; };   // == lzani_pair_t
+uint64_t filter_blocks(uint64_t n_pairs);
+cudaError_t launch_filter_count(cudaStream_t st, const FilterArgs& A, uint8_t* flags, uint32_t* blk_cnt,
+                                unsigned long long* blk_off, unsigned long long* n_missing);
+cudaError_t launch_filter_emit(cudaStream_t st, const FilterArgs& A, const uint8_t* flags,
+                               const unsigned long long* blk_off, PairOut* out, uint64_t cap);
 
 }  // namespace lzani

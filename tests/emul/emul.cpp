@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../lz-ani_b200/csrc/parse_core.h"
+#include "../../lz-ani_b200/csrc/outfilter.h"
 
 using namespace lzani;
 
@@ -167,4 +168,15 @@ extern "C" int lzani_emul_regions(const int32_t* p8, const uint8_t* ref3, uint32
         o[0] = g.ref_start; o[1] = g.ref_end; o[2] = g.seq_start; o[3] = g.seq_end; o[4] = g.num_matches; o[5] = g.num_mismatches;
     }
     return (int)out.v.size();
+}
+
+// The --out-filter decision of postproc.cu's F1 kernel (outfilter.h) for n unordered pairs, on the host:
+// thr = gani, ani, tani, qcov, rcov; ab/ba = n x 3 results; masks[i] = line bits.
+extern "C" void lzani_emul_out_filter(const double* thr, uint64_t n, const int32_t* ab, const int32_t* ba,
+                                      const uint32_t* len_a, const uint32_t* len_b, uint32_t* masks)
+{
+    const OutFilter f{thr[0], thr[1], thr[2], thr[3], thr[4]};
+    for (uint64_t i = 0; i < n; ++i)
+        masks[i] = out_filter_mask(f, DirStats{ab[3 * i], ab[3 * i + 1], ab[3 * i + 2]},
+                                   DirStats{ba[3 * i], ba[3 * i + 1], ba[3 * i + 2]}, len_a[i], len_b[i]);
 }

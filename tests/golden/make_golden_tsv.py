@@ -25,6 +25,12 @@ CASES = {
     "vir61_alt_complete": (["--in-dir", "test/vir61"], ALT + ["--out-format", "complete"], None),
     "example_default": (["--in-fasta", "example/multifasta.fna"], [], "example/output/ani.tsv"),
     "example_filter09": (["--in-fasta", "example/multifasta.fna"], ["--flt-kmerdb", "example/fltr.txt", "0.9"], None),
+    # --out-filter (lz_matcher.cpp:451-462): the device-side pre-filter of lzani_filter_pairs must keep exactly these lines
+    "vir61_outfilter": (["--in-dir", "test/vir61"], ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"], None),
+    "example_outfilter": (["--in-fasta", "example/multifasta.fna"],
+                          ["--out-filter", "tani", "0.85", "--out-filter", "rcov", "0.9", "--out-filter", "gani", "0.8"], None),
+    "example_filter09_outfilter": (["--in-fasta", "example/multifasta.fna"],
+                                   ["--flt-kmerdb", "example/fltr.txt", "0.9", "--out-filter", "ani", "0.97"], None),
 }
 
 

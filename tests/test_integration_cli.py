@@ -66,9 +66,20 @@ def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
     ("vir61_alt_complete", "vir61", ALT + ["--out-format", "complete"]),
     ("example_default", "example", []),
     ("example_filter09", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9"]),
+    # --out-filter: pairing + filter arithmetic on the device (lzani_filter_pairs), survivors only reach the host
+    ("vir61_outfilter", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
+    ("example_outfilter", "example", ["--out-filter", "tani", "0.85", "--out-filter", "rcov", "0.9", "--out-filter", "gani", "0.8"]),
+    ("example_filter09_outfilter", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
+    # the same with the rows dealt over two contexts that read each other's results in place
+    ("vir61_outfilter@2ctx", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
+    ("example_filter09_outfilter@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
 ])
 def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     need_cli()
+    env = dict(os.environ)
+    if case.endswith("@2ctx"):
+        case = case[:-5]
+        env["LZANI_DEVICES"] = "0,0"
     ss = mg.get_set(setname)
     order = None
     if "--flt-kmerdb" in extra:
@@ -80,7 +91,7 @@ def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     write_fasta(fa, ss, order)
     out = tmp_path / "ani.tsv"
     r = subprocess.run([CLI, "all2all", "--in-fasta", str(fa), "--out", str(out), "-V", "1"] + extra,
-                       capture_output=True, text=True)
+                       capture_output=True, text=True, env=env)
     assert r.returncode == 0, r.stderr
     want_tsv, want_ids = golden(case)
     assert open(out, "rb").read() == want_tsv
