@@ -93,6 +93,7 @@ typedef struct lzani_timing_t {
     uint32_t n_batches; /* reference batches the index memory budget forced       */
     double filter_ms;   /* lzani_filter_pairs: tables H2D, F1-F3, surviving pairs D2H */
     uint64_t filter_d2h_bytes; /* bytes lzani_filter_pairs copied device->host    */
+    double pairlist_ms; /* lzani_build_pair_list: edges H2D, expand, sort, CSR, D2H  */
 } lzani_timing_t;
 
 enum {
@@ -117,6 +118,14 @@ int lzani_create(lzani_ctx** ctx, const lzani_params_t* params, const int* devic
  * byte high-aligned), len[i] = number of bases.  The bytes are copied; the caller may free
  * them after the call returns.  May be called again to replace the set. */
 int lzani_set_sequences(lzani_ctx* ctx, uint32_t n, const uint8_t* const* data, const uint32_t* len);
+
+/* Device-side ingest: the same hand-off one step earlier in the loader.  text[i] = the
+ * symbols of sequence i exactly as CSeqReservoir::append receives them (seq_reservoir.cpp:18-87): one
+ * byte per base, FASTA letters in either case, anything that is not ACGTacgt -- N, IUPAC codes, the
+ * byte-5 contig separators load_fasta inserts (:110-127) -- is N (dna_code, seq_reservoir.h:243-247).
+ * The device builds the bit-plane records and the reverse complement straight from the text; the
+ * host never packs base-6 triples.  Results are identical to lzani_set_sequences on append's output. */
+int lzani_set_sequences_text(lzani_ctx* ctx, uint32_t n, const uint8_t* const* text, const uint32_t* len);
 
 /* Replaces the whole worker loop of do_matching (lz_matcher.cpp:192-269).
  * CSR pair list: for reference r in [0, n_refs) the queries are
@@ -166,6 +175,20 @@ int lzani_run_rows_resident(lzani_ctx* ctx, uint32_t n_rows, const uint32_t* ref
  * every CSR row; a missing opposite direction is an error (the reference asserts, :417). */
 int lzani_filter_pairs(lzani_ctx* ctx, lzani_ctx* const* group, int n_group, const uint32_t* eff_len,
                        const lzani_out_filter_t* flt, lzani_pair_t* pairs, uint64_t cap, uint64_t* n_out);
+
+/* Replaces the symmetric closure of CFilter::load_filter (filter.cpp:243-280) and CFilter::reorder_items
+ * (:293-345) -- the construction of the sparse pair list from the edges of a kmer-db filter file
+ * (SURVEY 8f-4).  edge_i[e], edge_j[e]: 0-based ids, in the file's own sequence order, of the e-th
+ * entry that passed the threshold (row i of the file lists `j+1:value`, filter.cpp:64-84); every edge
+ * is entered in both rows, as the reference does.  reorder_map[old id] = new id (the permutation
+ * CSeqReservoir::reorder_items returns, seq_reservoir.cpp:215-251; NULL = identity).  Output: the CSR
+ * pair list lzani_run takes -- row_off[n + 1], q_ids[*n_entries = 2 * n_edges], ids ascending within
+ * each row (the reference's in-row order is thread-arrival order and unobservable).  The multiset of
+ * (row, query) entries is the reference's: nothing is deduplicated or dropped.  When 2 * n_edges > cap
+ * nothing is written and LZANI_ERR_NOMEM is returned. */
+int lzani_build_pair_list(lzani_ctx* ctx, uint32_t n, uint64_t n_edges, const uint32_t* edge_i,
+                          const uint32_t* edge_j, const uint32_t* reorder_map, uint64_t* row_off,
+                          uint32_t* q_ids, uint64_t cap, uint64_t* n_entries);
 
 int lzani_get_timing(const lzani_ctx* ctx, lzani_timing_t* t);
 

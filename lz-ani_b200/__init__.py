@@ -34,7 +34,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "capi.cu")]
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "pairlist.cu", "capi.cu")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "regions.h", "simt.h", "outfilter.h")] + [
         os.path.join(ROOT, "include", "lzani_b200.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
@@ -50,7 +50,7 @@ class TimingStruct(C.Structure):
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("n_pairs", C.c_uint64), ("q_bases", C.c_uint64),
                 ("r_bases", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("launches", C.c_uint32), ("n_batches", C.c_uint32),
-                ("filter_ms", C.c_double), ("filter_d2h_bytes", C.c_uint64)]
+                ("filter_ms", C.c_double), ("filter_d2h_bytes", C.c_uint64), ("pairlist_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -76,11 +76,13 @@ def load_library() -> C.CDLL:
     lib.lzani_abi_version.restype = C.c_int
     lib.lzani_create.argtypes = [C.POINTER(vp), vp, vp, C.c_int]
     lib.lzani_set_sequences.argtypes = [vp, u32, vp, vp]
+    lib.lzani_set_sequences_text.argtypes = [vp, u32, vp, vp]
     lib.lzani_run.argtypes = [vp, u32, vp, vp, vp]
     lib.lzani_run_rows.argtypes = [vp, u32, vp, vp, vp, vp]
     lib.lzani_run_rows_resident.argtypes = [vp, u32, vp, vp, vp, C.c_int, vp]
     lib.lzani_run_rows_regions.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, u64, vp]
     lib.lzani_filter_pairs.argtypes = [vp, vp, C.c_int, vp, vp, vp, u64, vp]
+    lib.lzani_build_pair_list.argtypes = [vp, u32, u64, vp, vp, vp, vp, vp, u64, vp]
     lib.lzani_get_timing.argtypes = [vp, C.POINTER(TimingStruct)]
     lib.lzani_set_index_budget.argtypes = [vp, u64]
     lib.lzani_last_error.argtypes = [vp]
@@ -136,6 +138,19 @@ class Matcher:
             ptrs[i] = p.ctypes.data
         lens = np.ascontiguousarray(ss.lens, dtype=np.uint32)
         self._check(self.lib.lzani_set_sequences(self.h, n, ptrs, lens.ctypes.data), "lzani_set_sequences")
+        self.n = n
+
+    def set_sequences_text(self, texts):
+        """Device-side ingest (lzani_set_sequences_text): texts[i] = bytes / uint8 array, one byte per base,
+        as CSeqReservoir::append receives the sequence (seq_reservoir.cpp:18-87)."""
+        arrs = [np.frombuffer(t, dtype=np.uint8) if isinstance(t, (bytes, bytearray)) else np.ascontiguousarray(t, dtype=np.uint8)
+                for t in texts]
+        n = len(arrs)
+        ptrs = (C.c_void_p * max(n, 1))()
+        for i, a in enumerate(arrs):
+            ptrs[i] = a.ctypes.data if a.size else None
+        lens = np.array([a.size for a in arrs], dtype=np.uint32)
+        self._check(self.lib.lzani_set_sequences_text(self.h, n, ptrs, lens.ctypes.data), "lzani_set_sequences_text")
         self.n = n
 
     def timing(self) -> dict:
@@ -240,5 +255,28 @@ def _filter_pairs(self, eff_len, flt: dict, group=None, cap: int = 1 << 12):
 
 
 Matcher.filter_pairs = _filter_pairs
+
+
+def _build_pair_list(self, n: int, edge_i, edge_j, reorder_map=None):
+    """Sparse pair list on the device (lzani_build_pair_list; replaces the symmetric closure and id
+    remap of CFilter, filter.cpp:243-345).  Returns (row_off[n+1] uint64, q_ids uint32)."""
+    edge_i = np.ascontiguousarray(edge_i, dtype=np.uint32)
+    edge_j = np.ascontiguousarray(edge_j, dtype=np.uint32)
+    assert edge_i.size == edge_j.size
+    mp = None
+    if reorder_map is not None:
+        reorder_map = np.ascontiguousarray(reorder_map, dtype=np.uint32)
+        assert reorder_map.size == n
+        mp = reorder_map.ctypes.data
+    row_off = np.zeros(n + 1, dtype=np.uint64)
+    q_ids = np.zeros(max(2 * edge_i.size, 1), dtype=np.uint32)
+    n_ent = C.c_uint64(0)
+    self._check(self.lib.lzani_build_pair_list(self.h, n, edge_i.size, edge_i.ctypes.data, edge_j.ctypes.data, mp,
+                                               row_off.ctypes.data, q_ids.ctypes.data, q_ids.size, C.byref(n_ent)),
+                "lzani_build_pair_list")
+    return row_off, q_ids[: int(n_ent.value)].copy()
+
+
+Matcher.build_pair_list = _build_pair_list
 
 from .sharding import shard_rows  # noqa: E402,F401

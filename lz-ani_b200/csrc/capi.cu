@@ -191,7 +191,25 @@ extern "C" int lzani_get_timing(const lzani_ctx* c, lzani_timing_t* t)
     return LZANI_OK;
 }
 
+namespace {
+int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len, bool ascii);
+}
+
 extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len)
+{
+    return set_sequences_impl(c, n, data, len, false);
+}
+
+extern "C" int lzani_set_sequences_text(lzani_ctx* c, uint32_t n, const uint8_t* const* text, const uint32_t* len)
+{
+    return set_sequences_impl(c, n, text, len, true);
+}
+
+namespace {
+// bytes of one sequence in the staging buffer: base-6 triples, or one byte per base (16-byte aligned starts)
+inline uint64_t src_bytes_of(uint32_t len, bool ascii) { return ascii ? (((uint64_t)len + 15) & ~15ull) : ((uint64_t)len + 2) / 3; }
+
+int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len, bool ascii)
 {
     if (!c) return LZANI_ERR_ARG;
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
@@ -214,7 +232,7 @@ extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* cons
         meta[i].r_rec = recs + (uint64_t)q_form_recs((int)len[i], P.mrd);
         rec_base[i] = recs;
         recs = meta[i].r_rec + (uint64_t)r_form_recs((int)len[i], P.mrd);
-        src_bytes += ((uint64_t)len[i] + 2) / 3;
+        src_bytes += src_bytes_of(len[i], ascii);
     }
     rec_base[n] = recs;
 
@@ -222,7 +240,7 @@ extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* cons
     uint8_t* h_src = nullptr;
     LZ_CUDA(c, cudaMallocHost((void**)&h_src, src_bytes ? src_bytes : 1));
     for (uint32_t i = 0; i < n; ++i)
-        if (len[i]) memcpy(h_src + meta[i].src_off, data[i], ((size_t)len[i] + 2) / 3);
+        if (len[i]) memcpy(h_src + meta[i].src_off, data[i], ascii ? (size_t)len[i] : ((size_t)len[i] + 2) / 3);
 
     int rc = LZANI_OK;
     do {
@@ -237,7 +255,7 @@ extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* cons
         LZ_TRY(cudaMemcpyAsync(c->d_meta, meta.data(), sizeof(SeqMeta) * n, cudaMemcpyHostToDevice, c->stream));
         LZ_TRY(cudaMemcpyAsync(c->d_rec_base, rec_base.data(), sizeof(uint64_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, c->stream));
         LZ_TRY(cudaEventRecord(c->ev[1], c->stream));
-        LZ_TRY(launch_pack(c->stream, c->d_src, c->d_meta, c->d_rec_base, n, recs, P.mrd, c->d_recs));
+        LZ_TRY(launch_pack(c->stream, c->d_src, c->d_meta, c->d_rec_base, n, recs, P.mrd, c->d_recs, ascii));
         LZ_TRY(cudaEventRecord(c->ev[2], c->stream));
         LZ_TRY(cudaStreamSynchronize(c->stream));
 #undef LZ_TRY
@@ -256,6 +274,7 @@ extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* cons
     c->timing.launches = recs ? 1 : 0;
     return LZANI_OK;
 }
+}  // namespace
 
 namespace {
 
@@ -601,5 +620,63 @@ extern "C" int lzani_filter_pairs(lzani_ctx* c, lzani_ctx* const* group, int n_g
     c->timing.filter_ms = ms_between(c->ev[0], c->ev[1]);
     c->timing.filter_d2h_bytes = sizeof(PairOut) * total + 16;
     c->timing.launches += nb ? 3 : 1;
+    return LZANI_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// the sparse pair list built on the device.
+extern "C" int lzani_build_pair_list(lzani_ctx* c, uint32_t n, uint64_t n_edges, const uint32_t* edge_i,
+                                     const uint32_t* edge_j, const uint32_t* reorder_map, uint64_t* row_off,
+                                     uint32_t* q_ids, uint64_t cap, uint64_t* n_entries)
+{
+    if (!c) return LZANI_ERR_ARG;
+    if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
+    if (!row_off || !n_entries || (n_edges && (!edge_i || !edge_j))) return fail(c, LZANI_ERR_ARG, "edge / row_off / n_entries == NULL");
+    const uint64_t n_keys = 2 * n_edges;
+    *n_entries = n_keys;
+    if (n_keys > cap) return fail(c, LZANI_ERR_NOMEM, "q_ids buffer too small: " + std::to_string(n_keys) + " entries");
+    if (n_keys && !q_ids) return fail(c, LZANI_ERR_ARG, "q_ids == NULL");
+    LZ_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    int end_bit = 32 + ceil_log2_u64((uint64_t)(n > 1 ? n : 2));
+    if (end_bit > 64) end_bit = 64;
+    const size_t scratch_bytes = pairlist_sort_scratch_bytes(n_keys, end_bit);
+
+    uint32_t *d_i = nullptr, *d_j = nullptr, *d_map = nullptr, *d_q = nullptr;
+    unsigned long long *d_ka = nullptr, *d_kb = nullptr, *d_off = nullptr;
+    void* d_scratch = nullptr;
+    int rc = LZANI_OK;
+    unsigned long long bad = 0;
+    do {
+        cudaError_t e;
+#define LZ_TRY(call) if ((e = (call)) != cudaSuccess) { rc = fail(c, e == cudaErrorMemoryAllocation ? LZANI_ERR_NOMEM : LZANI_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e)); break; }
+        LZ_TRY(cudaMalloc((void**)&d_i, sizeof(uint32_t) * (n_edges ? n_edges : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_j, sizeof(uint32_t) * (n_edges ? n_edges : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_map, sizeof(uint32_t) * (n ? n : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_q, sizeof(uint32_t) * (n_keys ? n_keys : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_ka, sizeof(unsigned long long) * (n_keys ? n_keys : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_kb, sizeof(unsigned long long) * (n_keys ? n_keys : 1)));
+        LZ_TRY(cudaMalloc((void**)&d_off, sizeof(unsigned long long) * ((size_t)n + 1)));
+        LZ_TRY(cudaMalloc(&d_scratch, scratch_bytes ? scratch_bytes : 1));
+        LZ_TRY(cudaEventRecord(c->ev[0], st));
+        if (n_edges) {
+            LZ_TRY(cudaMemcpyAsync(d_i, edge_i, sizeof(uint32_t) * n_edges, cudaMemcpyHostToDevice, st));
+            LZ_TRY(cudaMemcpyAsync(d_j, edge_j, sizeof(uint32_t) * n_edges, cudaMemcpyHostToDevice, st));
+        }
+        if (reorder_map && n) LZ_TRY(cudaMemcpyAsync(d_map, reorder_map, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, st));
+        LZ_TRY(cudaMemsetAsync(c->d_reg_counter, 0, sizeof(unsigned long long), st));
+        LZ_TRY(launch_pairlist(st, d_i, d_j, n_edges, reorder_map ? d_map : nullptr, n, d_ka, d_kb, d_scratch, scratch_bytes,
+                               end_bit, d_off, d_q, c->d_reg_counter));
+        LZ_TRY(cudaMemcpyAsync(row_off, d_off, sizeof(uint64_t) * ((size_t)n + 1), cudaMemcpyDeviceToHost, st));
+        if (n_keys) LZ_TRY(cudaMemcpyAsync(q_ids, d_q, sizeof(uint32_t) * n_keys, cudaMemcpyDeviceToHost, st));
+        LZ_TRY(cudaMemcpyAsync(&bad, c->d_reg_counter, sizeof(bad), cudaMemcpyDeviceToHost, st));
+        LZ_TRY(cudaEventRecord(c->ev[1], st));
+        LZ_TRY(cudaStreamSynchronize(st));
+#undef LZ_TRY
+    } while (0);
+    cudaFree(d_i); cudaFree(d_j); cudaFree(d_map); cudaFree(d_q); cudaFree(d_ka); cudaFree(d_kb); cudaFree(d_off); cudaFree(d_scratch);
+    if (rc != LZANI_OK) return rc;
+    if (bad) return fail(c, LZANI_ERR_ARG, std::to_string(bad) + " edges name a sequence id >= n");
+    c->timing.pairlist_ms = ms_between(c->ev[0], c->ev[1]);
     return LZANI_OK;
 }

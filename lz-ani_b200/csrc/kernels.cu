@@ -1,6 +1,7 @@
 // kernels.cu -- the three sm_100a kernels of the LZ-ANI pair path.
 //
-//   K1 k_pack_sequences : reservoir bytes (three_in_byte) -> Q-form / R-form bit-plane records
+//   K1 k_pack_sequences : reservoir bytes (three_in_byte) or the loader's text (one byte per base)
+//                         -> Q-form / R-form bit-plane records
 //   K2 k_build_index    : per reference row, anchor presence bitmap + anchor table
 //   K3 k_parse_pairs    : persistent grid, one warp per ordered pair (parse_core.h)
 //
@@ -28,6 +29,7 @@ __device__ __forceinline__ uint32_t find_segment(const T* __restrict__ prefix, u
 // ------------------------------------------------------------------------------------------
 // K1.  One thread per output record.  rec_base[s] = first record of sequence s (its Q-form,
 // directly followed by its R-form).
+template <class Sym>
 __global__ void __launch_bounds__(256)
 k_pack_sequences(const uint8_t* __restrict__ src, const SeqMeta* __restrict__ meta,
                  const uint64_t* __restrict__ rec_base, uint32_t n_seqs, uint64_t n_recs, int mrd,
@@ -40,8 +42,9 @@ k_pack_sequences(const uint8_t* __restrict__ src, const SeqMeta* __restrict__ me
     const uint32_t local = (uint32_t)(t - m.q_rec);
     const uint32_t nq = (uint32_t)(m.r_rec - m.q_rec);
     Rec o;
-    if (local < nq) o = pack_q_record(src + m.src_off, m.len, local);
-    else o = pack_r_record(src + m.src_off, m.len, (uint32_t)mrd, local - nq);
+    const Sym sym{src + m.src_off};
+    if (local < nq) o = pack_q_record_from(sym, m.len, local);
+    else o = pack_r_record_from(sym, m.len, (uint32_t)mrd, local - nq);
     reinterpret_cast<uint4*>(recs)[t] = make_uint4(o.x, o.y, o.z, o.w);
 }
 
@@ -188,11 +191,12 @@ k_parse_regions(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 // ------------------------------------------------------------------------------------------
 // launch wrappers (called by capi.cu)
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* src, const SeqMeta* meta, const uint64_t* rec_base,
-                        uint32_t n_seqs, uint64_t n_recs, int mrd, Rec* recs)
+                        uint32_t n_seqs, uint64_t n_recs, int mrd, Rec* recs, bool ascii)
 {
     if (!n_recs) return cudaSuccess;
     const uint64_t blocks = (n_recs + 255) / 256;
-    k_pack_sequences<<<(unsigned)blocks, 256, 0, st>>>(src, meta, rec_base, n_seqs, n_recs, mrd, recs);
+    if (ascii) k_pack_sequences<SymAscii><<<(unsigned)blocks, 256, 0, st>>>(src, meta, rec_base, n_seqs, n_recs, mrd, recs);
+    else k_pack_sequences<SymPacked3><<<(unsigned)blocks, 256, 0, st>>>(src, meta, rec_base, n_seqs, n_recs, mrd, recs);
     return cudaGetLastError();
 }
 

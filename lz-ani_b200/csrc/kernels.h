@@ -15,7 +15,7 @@
 namespace lzani {
 
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* src, const SeqMeta* meta, const uint64_t* rec_base,
-                        uint32_t n_seqs, uint64_t n_recs, int mrd, Rec* recs);
+                        uint32_t n_seqs, uint64_t n_recs, int mrd, Rec* recs, bool ascii = false);
 
 cudaError_t launch_build_index(cudaStream_t st, const Rec* recs, const SeqMeta* meta, const uint32_t* row_ref,
                                const RefIndex* row_idx, const uint32_t* blk_base, uint32_t n_rows,
@@ -56,5 +56,12 @@ cudaError_t launch_filter_count(cudaStream_t st, const FilterArgs& A, uint8_t* f
                                 unsigned long long* blk_off, unsigned long long* n_missing);
 cudaError_t launch_filter_emit(cudaStream_t st, const FilterArgs& A, const uint8_t* flags,
                                const unsigned long long* blk_off, PairOut* out, uint64_t cap);
+
+// ---- pairlist.cu: kmer-db edges -> symmetric, id-remapped, row-sorted CSR pair list
+size_t pairlist_sort_scratch_bytes(uint64_t n_keys, int end_bit);
+cudaError_t launch_pairlist(cudaStream_t st, const uint32_t* ei, const uint32_t* ej, uint64_t n_edges,
+                            const uint32_t* map, uint32_t n, unsigned long long* keys_a, unsigned long long* keys_b,
+                            void* scratch, size_t scratch_bytes, int end_bit, unsigned long long* row_off,
+                            uint32_t* q_ids, unsigned long long* n_bad);
 
 }  // namespace lzani

@@ -164,21 +164,39 @@ LZ_HD uint32_t sym_at(const uint8_t* src, uint32_t j)
     return r == 0 ? b / 36u : (r == 1 ? (b / 6u) % 6u : b % 6u);
 }
 
-LZ_HD Rec pack_q_record(const uint8_t* src, uint32_t len, uint32_t rec)
+// symbol sources: the reservoir's base-6 triples, or the loader's one-byte-per-base text as
+// CSeqReservoir::append receives it (seq_reservoir.cpp:18-87; dna_code :243-247: ACGT in either case
+// = 0..3, every other byte -- N, IUPAC codes, the byte-5 contig separator of load_fasta :110-127 -- = N)
+struct SymPacked3 {
+    const uint8_t* src;
+    LZ_HD uint32_t operator()(uint32_t j) const { return sym_at(src, j); }
+};
+struct SymAscii {
+    const uint8_t* src;
+    LZ_HD uint32_t operator()(uint32_t j) const
+    {
+        const uint32_t ch = (uint32_t)src[j] | 0x20u;
+        return ch == 'a' ? 0u : ch == 'c' ? 1u : ch == 'g' ? 2u : ch == 't' ? 3u : 5u;
+    }
+};
+
+template <class Sym>
+LZ_HD Rec pack_q_record_from(Sym sym, uint32_t len, uint32_t rec)
 {
     Rec o; o.x = o.y = 0; o.z = 0; o.w = 0;
     const uint32_t base = rec * 32u;
     for (uint32_t j = 0; j < 32u; ++j) {
         const uint32_t p = base + j;
         uint32_t c = 5;
-        if (p < len) c = sym_at(src, p);
+        if (p < len) c = sym(p);
         if (c < 4) { o.x |= (c & 1u) << j; o.y |= (c >> 1) << j; }
         else o.z |= 1u << j;
     }
     return o;
 }
 
-LZ_HD Rec pack_r_record(const uint8_t* src, uint32_t len, uint32_t mrd, uint32_t rec)
+template <class Sym>
+LZ_HD Rec pack_r_record_from(Sym sym, uint32_t len, uint32_t mrd, uint32_t rec)
 {
     Rec o; o.x = o.y = 0; o.z = 0; o.w = 0;
     const uint32_t base = rec * 32u;
@@ -186,15 +204,21 @@ LZ_HD Rec pack_r_record(const uint8_t* src, uint32_t len, uint32_t mrd, uint32_t
     for (uint32_t j = 0; j < 32u; ++j) {
         const uint32_t p = base + j;
         uint32_t c = 5;
-        if (p < len) c = sym_at(src, p);
+        if (p < len) c = sym(p);
         else if (p >= rc0 && p < rc0 + len) {
-            c = sym_at(src, len - 1u - (p - rc0));
+            c = sym(len - 1u - (p - rc0));
             if (c < 4) c = 3u - c;
         }
         if (c < 4) { o.x |= (c & 1u) << j; o.y |= (c >> 1) << j; }
         else o.z |= 1u << j;
     }
     return o;
+}
+
+LZ_HD Rec pack_q_record(const uint8_t* src, uint32_t len, uint32_t rec) { return pack_q_record_from(SymPacked3{src}, len, rec); }
+LZ_HD Rec pack_r_record(const uint8_t* src, uint32_t len, uint32_t mrd, uint32_t rec)
+{
+    return pack_r_record_from(SymPacked3{src}, len, mrd, rec);
 }
 
 // ------------------------------------------------------------------------------------------

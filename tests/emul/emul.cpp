@@ -180,3 +180,21 @@ extern "C" void lzani_emul_out_filter(const double* thr, uint64_t n, const int32
         masks[i] = out_filter_mask(f, DirStats{ab[3 * i], ab[3 * i + 1], ab[3 * i + 2]},
                                    DirStats{ba[3 * i], ba[3 * i + 1], ba[3 * i + 2]}, len_a[i], len_b[i]);
 }
+
+// K1's element functions on the host: the Q-form and R-form records of one sequence from either symbol
+// source (ascii = 0: three_in_byte bytes; 1: the loader's text, one byte per base).
+extern "C" void lzani_emul_pack_records(const uint8_t* src, uint32_t len, int mrd, int ascii, uint32_t* q_out, uint32_t* r_out)
+{
+    const int nq = q_form_recs((int)len, mrd), nr = r_form_recs((int)len, mrd);
+    for (int i = 0; i < nq; ++i) {
+        const Rec o = ascii ? pack_q_record_from(SymAscii{src}, len, (uint32_t)i) : pack_q_record_from(SymPacked3{src}, len, (uint32_t)i);
+        memcpy(q_out + 4 * i, &o, 16);
+    }
+    for (int i = 0; i < nr; ++i) {
+        const Rec o = ascii ? pack_r_record_from(SymAscii{src}, len, (uint32_t)mrd, (uint32_t)i)
+                            : pack_r_record_from(SymPacked3{src}, len, (uint32_t)mrd, (uint32_t)i);
+        memcpy(r_out + 4 * i, &o, 16);
+    }
+}
+extern "C" int lzani_emul_q_recs(uint32_t len, int mrd) { return q_form_recs((int)len, mrd); }
+extern "C" int lzani_emul_r_recs(uint32_t len, int mrd) { return r_form_recs((int)len, mrd); }

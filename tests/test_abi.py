@@ -32,7 +32,7 @@ def test_library_builds_and_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     # lzani_result_t == results_t: three int32 (defs.h:48-65); lzani_params_t: eight int32
     assert np.dtype(np.int32).itemsize * 3 == 12
-    assert C.sizeof(lz.TimingStruct) == 6 * 8 + 5 * 8 + 2 * 4 + 2 * 8
+    assert C.sizeof(lz.TimingStruct) == 6 * 8 + 5 * 8 + 2 * 4 + 3 * 8
     assert lz.PAIR_DTYPE.itemsize == 36          # lzani_pair_t: 2 x u32 + 2 x results_t + u32
 
 
