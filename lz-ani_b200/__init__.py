@@ -25,7 +25,8 @@ from . import hostio, sharding, synth  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "liblzani_b200.so")
+# LZANI_LIB: an alternative build of the same library (kernel tuning experiments, tools/variants.sh)
+LIB_PATH = os.environ.get("LZANI_LIB") or os.path.join(_HERE, "liblzani_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

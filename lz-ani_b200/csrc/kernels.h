@@ -7,7 +7,9 @@
 #include "regions.h"
 #include "outfilter.h"
 
+#ifndef LZ_PARSE_THREADS
 #define LZ_PARSE_THREADS 128
+#endif
 #ifndef LZ_PARSE_MIN_BLOCKS
 #define LZ_PARSE_MIN_BLOCKS 5
 #endif

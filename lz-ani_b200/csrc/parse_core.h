@@ -587,7 +587,9 @@ LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const PT& P)
 // mask Mis_m of the 96-base reference window against that base; a seed at (k, x) is a 0 bit x of
 //   S_k = Mis_k | Mis_{k+1}>>1 | ... | Mis_{k+6}>>6   (built by doubling: pairs, fours, 4+3).
 // Returns the first k with a seed, 64 when there is none in [0, K], -1 when not applicable (an N
-// or the sequence end inside the window: left to the warp-cooperative path).
+// or the sequence end inside the window: left to the warp-cooperative path).  With a seed at k the
+// value also carries, in bits [8,15), the window offset x of its reference position P0+x when that
+// is the ONLY seed of position k (SPEC_MULTI set otherwise): best_seed() then has nothing to search.
 struct V3 { uint32_t a, b, c; };
 LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 32
 {
@@ -598,6 +600,7 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
     return r;
 }
 constexpr int SPEC_MAX_K = 57;
+constexpr int SPEC_MULTI = 1 << 15;
 constexpr int LZ_WIN_WORDS = 8;                    // hit-mask words per lane and window (8192 positions)
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 // per-warp scratch (shared memory on the device): the hit masks of the current window, one column
@@ -656,7 +659,12 @@ LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K
             a4[(u + 1) % 4] = p4;                                   // slot (m-3) mod 4
             mis_prev = mis;
             if (m >= 6) {
-                if ((~s7.a & m0) | (~s7.b & m1) | (~s7.c & m2)) return m - 6;
+                const uint32_t c0 = ~s7.a & m0, c1 = ~s7.b & m1, c2 = ~s7.c & m2;
+                if (c0 | c1 | c2) {
+                    const int x = c0 ? ctz32(c0) : (c1 ? 32 + ctz32(c1) : 64 + ctz32(c2));
+                    const bool multi = popc32(c0) + popc32(c1) + popc32(c2) > 1;
+                    return (m - 6) | (x << 8) | (multi ? SPEC_MULTI : 0);
+                }
                 m2 = (m2 << 1) | (m1 >> 31);
                 m1 = (m1 << 1) | (m0 >> 31);
                 m0 = (m0 << 1) | 1u;
@@ -922,6 +930,7 @@ LZ_COLD void best_seed(W& w, const PairView& pv, const PT& P, const Planes64& Q,
 // count -- the event is "virtual": LIVE | DEFER, evaluated by anchor_lookup() when taken.
 // need_pos: prediction mode, where an anchor at reference position 0 counts as none (:604).
 constexpr uint32_t HIT_RUN_SHIFT = 22;
+constexpr uint32_t HIT_X_SHIFT = 25;       // w2 [25,32): window offset of the first seed's reference position (w3 bit 31: not unique)
 struct Event { int j, qi, a_pos; uint32_t w2, w3; };
 template <class W, class LI, class LU>
 LZ_HD Event next_event(W& w, const LI& r_p, const LU& r_pos, const LU& r_w2, const LU& r_w3, int i0, int lim, bool need_pos)
@@ -984,7 +993,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     const int n_loop = Dq - P.msl;     // loop runs while i < n_loop (i + msl < Dq, :501)
     const int NC = 65 - P.msl;         // chunk size: msl-runs starting in the chunk fit 64 bits
 
-    int spec_i0 = -1, spec_K1 = 0, spec_ks = 64;   // speculative seed record of the match just taken
+    int spec_i0 = -1, spec_K1 = 0, spec_ks = 64, spec_x = -1;   // speculative seed record of the match just taken
     int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
     typename W::template Lanes<uint32_t> r_pos, r_w2, r_w3;
@@ -1119,7 +1128,10 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         int K = idx < b_cnt ? win_base + (int)(list[idx] & 0x1FFFu) - si0 : b_cover - 1 - si0;
                         if (K > P.mqd) K = P.mqd;
                         const int ks = spec_first_seed(pv, P, si0, sP0, K);
-                        if (ks >= 0) r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)ks << 24);
+                        if (ks >= 0) {
+                            r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
+                            r_w2[ln] |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;
+                        }
                     }
                 }
                 w.sync();
@@ -1190,6 +1202,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     spec_i0 = s.i;
                     spec_K1 = (int)((w3 >> 18) & 63u);
                     spec_ks = (int)((w3 >> 24) & 127u);
+                    spec_x = (w3 >> 31) ? -1 : (int)(w2 >> HIT_X_SHIFT);
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
                     lz_matches++; lz_fast++;
 #endif
@@ -1263,7 +1276,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             lz_spec_used++;
         }
 #endif
-        if (!use_spec || cand) Q = ext64(pv.q, i0);
+        if (!use_spec || (cand && spec_x < 0)) Q = ext64(pv.q, i0);
         if (!use_spec) {
             cand = diag_seed_starts(w, pv, P, Q, i0, P0, d_lo, d_hi) & low_mask64(ns);
         }
@@ -1275,7 +1288,21 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             const int qi = i0 + k;
             int best_pos = 0, best_len = 0;
             if (ks == k) {
-                best_seed(w, pv, P, Q, i0, P0, lit0, k, d_lo, d_hi, best_pos, best_len);
+                if (use_spec && spec_x >= 0) {
+                    // the record names the only seed of this position: measure it (equal_len, :192-207)
+                    best_pos = P0 + spec_x;
+                    const uint32_t m0 = mism32(pv.q, pv.Dq, qi, pv.r, pv.Dr, best_pos);
+                    best_len = m0 ? ctz32(m0) : equal_len_coop(w, pv, qi, best_pos, 32);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                    {   // TEST ONLY (tests/emul): must agree with the diagonal scan
+                        int cp = 0, cl = 0;
+                        const Planes64 Qc = ext64(pv.q, i0);
+                        best_seed(w, pv, P, Qc, i0, P0, lit0, k, d_lo, d_hi, cp, cl);
+                        if (cp != best_pos || cl != best_len) { lz_spec_mismatches++; best_pos = cp; best_len = cl; }
+                    }
+#endif
+                } else
+                    best_seed(w, pv, P, Q, i0, P0, lit0, k, d_lo, d_hi, best_pos, best_len);
                 cand &= cand - 1ull;
             }
             uint32_t w2 = 0, w3 = 0;
@@ -1325,6 +1352,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 spec_i0 = s.i;
                 spec_K1 = (int)((m_w3 >> 18) & 63u);
                 spec_ks = (int)((m_w3 >> 24) & 127u);
+                spec_x = (m_w3 >> 31) ? -1 : (int)(m_w2 >> HIT_X_SHIFT);
             }
         }
     }
