@@ -73,6 +73,10 @@ def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
     # the same with the rows dealt over two contexts that read each other's results in place
     ("vir61_outfilter@2ctx", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
     ("example_filter09_outfilter@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
+    # two GPUs (skipped on a one-GPU box): rows dealt r mod 2, the filter kernel reads the peer's rows over NVLink
+    ("vir61_default@2gpu", "vir61", []),
+    ("vir61_outfilter@2gpu", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
+    ("example_filter09_outfilter@2gpu", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
 ])
 def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     need_cli()
@@ -80,6 +84,12 @@ def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     if case.endswith("@2ctx"):
         case = case[:-5]
         env["LZANI_DEVICES"] = "0,0"
+    elif case.endswith("@2gpu"):
+        import torch
+        if torch.cuda.device_count() < 2:
+            pytest.skip("needs two GPUs")
+        case = case[:-5]
+        env["LZANI_DEVICES"] = "0,1"
     ss = mg.get_set(setname)
     order = None
     if "--flt-kmerdb" in extra:

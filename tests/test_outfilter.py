@@ -200,7 +200,9 @@ def test_filter_pairs_sparse_and_two_context_group():
     finally:
         m.close()
 
-    ms = [lz.Matcher(device=0), lz.Matcher(device=0)]
+    import torch
+    second = 1 if torch.cuda.device_count() >= 2 else 0      # two GPUs when the box has them: real peer access
+    ms = [lz.Matcher(device=0), lz.Matcher(device=second)]
     try:
         parts = []
         for g, mm in enumerate(ms):
