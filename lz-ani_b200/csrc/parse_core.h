@@ -601,6 +601,10 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
 }
 constexpr int SPEC_MAX_K = 57;
 constexpr int SPEC_MULTI = 1 << 15;
+#ifndef LZ_CHAIN
+#define LZ_CHAIN 0
+#endif
+constexpr bool kChain = LZ_CHAIN != 0;   // successor links (measured slower on B200: off)
 constexpr int LZ_WIN_WORDS = 8;                    // hit-mask words per lane and window (8192 positions)
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 // per-warp scratch (shared memory on the device): the hit masks of the current window, one column
@@ -610,7 +614,7 @@ struct WarpScratch {
     uint16_t list[32];
 };
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
-static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0, lz_why[12] = {0};   // TEST ONLY counters (tests/emul)
+static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0, lz_chain = 0, lz_why[12] = {0};   // TEST ONLY counters (tests/emul)
 #endif
 template <class PT>
 LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
@@ -993,24 +997,29 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     const int n_loop = Dq - P.msl;     // loop runs while i < n_loop (i + msl < Dq, :501)
     const int NC = 65 - P.msl;         // chunk size: msl-runs starting in the chunk fit 64 bits
 
-    int spec_i0 = -1, spec_K1 = 0, spec_ks = 64, spec_x = -1;   // speculative seed record of the match just taken
+    // speculative seed record of the match just taken; spec_K1 > 0 <=> it describes the window at s.i
+    // (cleared by every literal step)
+    int spec_K1 = 0, spec_ks = 64, spec_x = -1;
+    int chain_nx = 32;                 // its successor link (32: none)
     int win_base = 0, win_end = 0;     // hit masks cover [win_base, win_end)
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
     typename W::template Lanes<uint32_t> r_pos, r_w2, r_w3;
-    typename W::template Lanes<int> r_p;
+    typename W::template Lanes<int> r_p, r_nx;     // r_nx: successor links (see "successor links" below)
     LZ_EACH(w, ln)
     {
         for (int q = 0; q < LZ_WIN_WORDS; ++q) sc->hm[q][ln] = 0;
-        r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF;
+        r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; r_nx[ln] = 32;
     }
 
-    while (s.i < n_loop) {
+    for (;;) {
         const int i0 = s.i;
         // the match this step finds, if any (one take_match call site keeps the code small)
         bool matched = false;
         int m_qi = 0, m_lit = 0, m_pred = -1, m_pos = 0, m_len = 0;
         uint32_t m_w2 = 0, m_w3 = 0;
+        int m_j = -1;                  // batch record the match was taken from (when m_w2 != 0)
         if (i0 >= b_cover) {
+            if (i0 >= n_loop) break;       // b_cover <= n_loop: the end of the loop (:501) is only met here
             if (i0 >= win_end) {
                 // ---- new window: lane l probes positions win_base + LZ_WIN_LANE*l + [0, LZ_WIN_LANE)
                 // (large enough that batches of 32 hits are normally full: ~2.4 % of the positions of
@@ -1114,8 +1123,10 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             }
             w.sync();
             if (PT::kSpecSeeds && !RS::kActive && P.mqd <= SPEC_MAX_K) {
+                typename W::template Lanes<int> tc;      // the record the walk meets next if it takes this one
                 LZ_EACH(w, ln)
                 {
+                    tc[ln] = 32;
                     if (r_w2[ln] & HIT_FWD) {
                         // the prediction window this hit opens if it is taken (see spec_first_seed):
                         // scanned up to the next hit of the batch (inclusive) or the end of what the
@@ -1131,11 +1142,46 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         if (ks >= 0) {
                             r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
                             r_w2[ln] |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;
+                            // not when the walk would come to stand inside the run of the record before idx
+                            const int prev = idx - 1;
+                            const bool inside = prev > ln && win_base + (int)(list[prev] & 0x1FFFu) + (int)(list[prev] >> 13) >= si0;
+                            if (idx < b_cnt && !inside) tc[ln] = idx;
                         }
                     }
                 }
                 w.sync();
+                // ---- successor links.  If the walk takes record ln entirely from its fields (fast path),
+                // what happens next depends on nothing but the batch: the next record t it meets, and
+                // whether that is one of the two plain events of the fast path below (a distant anchor
+                // taken from ITS record, possibly after the prediction expired).  Lane ln decides that
+                // now, for all records at once; the walk then follows nx[] instead of searching.
+                if (kChain) {
+                typename W::template Lanes<uint32_t> t_w2, t_pos;
+                w.gather(t_w2, r_w2, tc);
+                w.gather(t_pos, r_pos, tc);
+                LZ_EACH(w, ln)
+                {
+                    int nx = 32;
+                    if (tc[ln] < 32 && (t_w2[ln] & (HIT_DEFER | HIT_FWD)) == HIT_FWD) {
+                        const uint32_t b = r_w2[ln], c = r_w3[ln];
+                        const int adv = (int)(b & 63u) + (int)((b >> 6) & 63u);
+                        const int si0 = r_p[ln] + adv, sP0 = (int)r_pos[ln] + adv;
+                        const int K1 = (int)((c >> 18) & 63u), ks = (int)((c >> 24) & 127u);
+                        const int ka = win_base + (int)(list[tc[ln]] & 0x1FFFu) - si0;
+                        bool ok;
+                        if (ka > P.mqd) ok = K1 > P.mqd && ks >= 64;           // the prediction expires first
+                        else {
+                            int dist = (int)t_pos[ln] - (sP0 + ka);
+                            if (dist < 0) dist = -dist;
+                            ok = ka < K1 && ks > ka && t_pos[ln] != 0u && dist > P.mrd;
+                        }
+                        if (ok) nx = tc[ln];
+                    }
+                    r_nx[ln] = nx;
+                }
+                }
             }
+            chain_nx = 32;
         }
 
         // ---- FAST PATH.  The walk stands right behind an anchor match taken from its record
@@ -1146,13 +1192,42 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         //   * nothing at all for mqd+1 positions: the prediction expires.
         // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
         // general code below, which re-derives the same step.
-        if (PT::kSpecSeeds && !RS::kActive && (s.pred < 0 || (s.lit == 0 && i0 == spec_i0 && spec_K1 > 0))) {
-            const Event ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
-            const int qi = ev.qi;
-            const int ka = qi - i0;
-            const uint32_t w2 = ev.w2;
-            const int a_pos = ev.a_pos;
-            bool plain = (w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
+        if (PT::kSpecSeeds && !RS::kActive && (s.pred < 0 || spec_K1 > 0)) {
+            Event ev;
+            bool plain;
+            int nx_next = -1;          // successor link of the event, when already fetched
+            const bool chained = kChain && chain_nx < 32 && s.pred >= 0;
+            if (chained) {
+                // the successor link of the record just taken: a plain event, decided in the batch stage
+                ev.j = chain_nx;
+                ev.qi = w.get(r_p, ev.j);
+                ev.w2 = w.get(r_w2, ev.j);
+                ev.w3 = w.get(r_w3, ev.j);
+                ev.a_pos = (int)w.get(r_pos, ev.j);
+                nx_next = w.get(r_nx, ev.j);
+                plain = true;
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                {   // TEST ONLY (tests/emul): the link must be what the search below finds
+                    Event e2 = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
+                    bool ok = e2.j >= 0 && (e2.w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;
+                    const int ka2 = e2.qi - i0;
+                    if (ok && ka2 > P.mqd) {
+                        ok = spec_K1 > P.mqd && spec_ks >= 64;
+                        if (ok) e2 = next_event(w, r_p, r_pos, r_w2, r_w3, i0 + P.mqd + 1, 0x7FFFFFFF, false);
+                        ok = ok && e2.j >= 0 && (e2.w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;
+                    } else if (ok) {
+                        int dist = e2.a_pos - (s.pred + ka2);
+                        if (dist < 0) dist = -dist;
+                        ok = ka2 < spec_K1 && spec_ks > ka2 && e2.a_pos != 0 && dist > P.mrd;
+                    }
+                    if (!ok || e2.j != ev.j || e2.qi != ev.qi) lz_spec_mismatches++;
+                    lz_chain++;
+                }
+#endif
+            } else {
+            ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
+            const int ka = ev.qi - i0;
+            plain = (ev.w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
             if (s.pred >= 0) {
                 if (ka > P.mqd) {
                     plain = false;
@@ -1161,16 +1236,22 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         s.i = i0 + P.mqd + 1;
                         s.lit = P.mqd + 1;
                         s.pred = -1;
+                        spec_K1 = 0;
                         continue;
                     }
                 } else {
-                    int dist = a_pos - (s.pred + ka);
+                    int dist = ev.a_pos - (s.pred + ka);
                     if (dist < 0) dist = -dist;
-                    plain = plain && ka < spec_K1 && spec_ks > ka && a_pos != 0 && dist > P.mrd;
+                    plain = plain && ka < spec_K1 && spec_ks > ka && ev.a_pos != 0 && dist > P.mrd;
                 }
             }
+            }
+            const int qi = ev.qi;
+            const uint32_t w2 = ev.w2;
+            const int a_pos = ev.a_pos;
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
             if (!plain) {   // TEST ONLY: why the fast path was left
+                const int ka = qi - i0;
                 if (ev.j < 0) lz_why[0]++;
                 else if (w2 & HIT_DEFER) lz_why[1]++;
                 else if (!(w2 & HIT_FWD)) lz_why[2]++;
@@ -1199,17 +1280,19 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     s.pred = a_pos + len + fwd;
                     s.lit = 0;
                     s.re = s.i;
-                    spec_i0 = s.i;
                     spec_K1 = (int)((w3 >> 18) & 63u);
                     spec_ks = (int)((w3 >> 24) & 127u);
                     spec_x = (w3 >> 31) ? -1 : (int)(w2 >> HIT_X_SHIFT);
+                    if (nx_next < 0) nx_next = w.get(r_nx, ev.j);
+                    chain_nx = spec_K1 > 0 ? nx_next : 32;
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
                     lz_matches++; lz_fast++;
 #endif
                     continue;
                 }
+                chain_nx = 32;             // backward record not usable: the general code takes this step
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
-                lz_why[8]++;               // backward record not usable
+                lz_why[8]++;
 #endif
             }
         }
@@ -1236,7 +1319,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             }
             if (a_len > 0 && a_len >= P.msl) {
                 matched = true;
-                m_qi = qi; m_lit = s.lit + (qi - i0); m_pred = -1; m_pos = a_pos; m_len = a_len; m_w2 = w2; m_w3 = w3;
+                m_qi = qi; m_lit = s.lit + (qi - i0); m_pred = -1; m_pos = a_pos; m_len = a_len; m_w2 = w2; m_w3 = w3; m_j = ev.j;
             } else {
                 s.lit += qi + 1 - i0;
                 s.i = qi + 1;
@@ -1252,7 +1335,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
         lz_pred_steps++;
 #endif
-        const bool use_spec = PT::kSpecSeeds && lit0 == 0 && i0 == spec_i0 && spec_K1 > 0;
+        const bool use_spec = PT::kSpecSeeds && spec_K1 > 0;
         if (use_spec && n > spec_K1) n = spec_K1;
         // the first anchor record inside the chunk that counts here (position 0 == "none", :604)
         const Event eva = next_event(w, r_p, r_pos, r_w2, r_w3, i0, i0 + n, true);
@@ -1330,7 +1413,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             }
             if (best_len >= P.msl) {
                 matched = true;
-                m_qi = qi; m_lit = lit0 + k; m_pred = P0 + lit0 + k; m_pos = best_pos; m_len = best_len; m_w2 = w2; m_w3 = w3;
+                m_qi = qi; m_lit = lit0 + k; m_pred = P0 + lit0 + k; m_pos = best_pos; m_len = best_len; m_w2 = w2; m_w3 = w3; m_j = ja;
                 break;
             }
             if (ja >= 0 && k == ka) break;       // the step ends at the anchor's position
@@ -1340,6 +1423,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             s.i = i0 + ns;
             s.lit = lit0 + ns;
             s.pred = s.lit > P.mqd ? -1 : s.pred + ns;
+            spec_K1 = 0;
         }
         }
         if (matched) {
@@ -1348,11 +1432,12 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             lz_matches++;
 #endif
             spec_K1 = 0;
+            chain_nx = 32;
             if (PT::kSpecSeeds && (m_w2 & HIT_FWD)) {    // s.i / s.pred came from the record
-                spec_i0 = s.i;
                 spec_K1 = (int)((m_w3 >> 18) & 63u);
                 spec_ks = (int)((m_w3 >> 24) & 127u);
                 spec_x = (m_w3 >> 31) ? -1 : (int)(m_w2 >> HIT_X_SHIFT);
+                if (spec_K1 > 0 && m_j >= 0) chain_nx = w.get(r_nx, m_j);
             }
         }
     }
