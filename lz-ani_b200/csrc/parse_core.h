@@ -605,7 +605,14 @@ constexpr int SPEC_MULTI = 1 << 15;
 #define LZ_CHAIN 0
 #endif
 constexpr bool kChain = LZ_CHAIN != 0;   // successor links (measured slower on B200: off)
-constexpr int LZ_WIN_WORDS = 8;                    // hit-mask words per lane and window (8192 positions)
+#ifndef LZ_SCAN_UNROLL
+#define LZ_SCAN_UNROLL 4
+#endif
+#ifndef LZ_WIN_WORDS_N
+#define LZ_WIN_WORDS_N 8
+#endif
+constexpr int kScanUnroll = LZ_SCAN_UNROLL;
+constexpr int LZ_WIN_WORDS = LZ_WIN_WORDS_N;                    // hit-mask words per lane and window (8192 positions)
 constexpr int LZ_WIN_LANE = 32 * LZ_WIN_WORDS;     // query positions per lane and window
 // per-warp scratch (shared memory on the device): the hit masks of the current window, one column
 // per lane, and the hit list of the current batch
@@ -1045,7 +1052,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                                 bad = (uint32_t)u;
                             }
 #if defined(__CUDA_ARCH__)
-#pragma unroll 4
+#pragma unroll kScanUnroll
 #endif
                             for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
                                 const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
