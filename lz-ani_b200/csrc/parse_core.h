@@ -1203,6 +1203,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             Event ev;
             bool plain;
             int nx_next = -1;          // successor link of the event, when already fetched
+            bool expired = false;      // the state moved on inside this step: i0 is stale
             const bool chained = kChain && chain_nx < 32 && s.pred >= 0;
             if (chained) {
                 // the successor link of the record just taken: a plain event, decided in the batch stage
@@ -1237,15 +1238,16 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             plain = (ev.w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
             if (s.pred >= 0) {
                 if (ka > P.mqd) {
-                    plain = false;
                     if (spec_K1 > P.mqd && spec_ks >= 64) {
-                        // mqd+1 literal steps, then the prediction is dropped (:699-707)
+                        // mqd+1 literal steps, then the prediction is dropped (:699-707) ...
                         s.i = i0 + P.mqd + 1;
                         s.lit = P.mqd + 1;
                         s.pred = -1;
                         spec_K1 = 0;
-                        continue;
-                    }
+                        // ... and the same event, still ahead (ka > mqd), is the next one without a prediction
+                        expired = true;
+                        if (!plain) continue;
+                    } else plain = false;
                 } else {
                     int dist = ev.a_pos - (s.pred + ka);
                     if (dist < 0) dist = -dist;
@@ -1298,6 +1300,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     continue;
                 }
                 chain_nx = 32;             // backward record not usable: the general code takes this step
+                if (expired) continue;
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
                 lz_why[8]++;
 #endif
