@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -63,6 +64,21 @@ struct lzani_ctx {
     uint32_t* d_eff_len = nullptr; uint64_t eff_cap = 0;
     PairOut* d_pairs = nullptr; uint64_t pairs_cap = 0;
 
+    // staged parse (kernels.cu "K3 staged"): two chunk slots, each with its own stream, so that one chunk's
+    // data-parallel stages fill the tail of the other chunk's walk
+    struct Slot {
+        StagedBufs B{};
+        uint64_t pairs_cap = 0, words_cap = 0, recs_cap = 0;
+        cudaStream_t st = nullptr;
+        cudaEvent_t done = nullptr;
+        uint32_t* h_total = nullptr;      // pinned: records of the chunk
+    } slot[2];
+    int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
+    uint64_t staged_words = 48ull << 20;  // words per chunk (LZANI_STAGED_WORDS)
+    int walk_blocks_per_sm = 1;
+    double rec_per_word = 1.0;            // observed hit runs per 32 query positions (chunk sizing)
+    uint32_t staged_chunks = 0;           // of the last run
+
     cudaEvent_t ev[8]{};
     lzani_timing_t timing{};
 };
@@ -101,6 +117,50 @@ void free_sequences(lzani_ctx* c)
     cudaFree(c->d_recs); c->d_recs = nullptr;
     c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
     c->last_valid = false;
+}
+
+void free_slot(lzani_ctx::Slot& s)
+{
+    cudaFree(s.B.desc); cudaFree(s.B.n_words); cudaFree(s.B.word_off); cudaFree(s.B.hm); cudaFree(s.B.rec_off);
+    cudaFree(s.B.list); cudaFree(s.B.recs); cudaFree(s.B.tmp); cudaFree(s.B.wpair);
+    s.B.desc = nullptr; s.B.n_words = nullptr; s.B.word_off = nullptr; s.B.hm = nullptr; s.B.rec_off = nullptr; s.B.wpair = nullptr;
+    s.B.list = nullptr; s.B.recs = nullptr; s.B.tmp = nullptr; s.B.tmp_bytes = 0;
+    s.pairs_cap = s.words_cap = s.recs_cap = 0;
+}
+
+// chunk scratch of one slot, grown on demand (the caller has synchronised the slot's stream)
+int ensure_slot(lzani_ctx* c, lzani_ctx::Slot& s, uint64_t pairs, uint64_t words, uint64_t recs)
+{
+    if (pairs > s.pairs_cap) {
+        cudaFree(s.B.desc); cudaFree(s.B.n_words); cudaFree(s.B.word_off);
+        s.B.desc = nullptr; s.B.n_words = nullptr; s.B.word_off = nullptr; s.pairs_cap = 0;
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.desc, sizeof(PairDesc) * pairs));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.n_words, sizeof(uint32_t) * (pairs + 1)));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.word_off, sizeof(uint32_t) * (pairs + 1)));
+        s.pairs_cap = pairs;
+    }
+    if (words > s.words_cap) {
+        cudaFree(s.B.hm); cudaFree(s.B.rec_off); cudaFree(s.B.wpair);
+        s.B.hm = nullptr; s.B.rec_off = nullptr; s.B.wpair = nullptr; s.words_cap = 0;
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.wpair, sizeof(uint32_t) * (words + 1)));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.hm, sizeof(uint32_t) * (words + 1)));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.rec_off, sizeof(uint32_t) * (words + 1)));
+        s.words_cap = words;
+    }
+    if (recs > s.recs_cap) {
+        cudaFree(s.B.list); cudaFree(s.B.recs);
+        s.B.list = nullptr; s.B.recs = nullptr; s.recs_cap = 0;
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.list, 8 * recs));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.recs, sizeof(Rec) * (recs + 1)));
+        s.recs_cap = recs;
+    }
+    const size_t tb = staged_scan_bytes(std::max(s.words_cap, s.pairs_cap) + 1);
+    if (tb > s.B.tmp_bytes) {
+        cudaFree(s.B.tmp); s.B.tmp = nullptr; s.B.tmp_bytes = 0;
+        LZ_CUDA(c, cudaMalloc(&s.B.tmp, tb));
+        s.B.tmp_bytes = tb;
+    }
+    return LZANI_OK;
 }
 
 float ms_between(cudaEvent_t a, cudaEvent_t b)
@@ -154,6 +214,15 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     LZ_CUDA(c, cudaMalloc((void**)&c->d_counter, sizeof(unsigned long long)));
     LZ_CUDA(c, cudaMalloc((void**)&c->d_reg_counter, sizeof(unsigned long long)));
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
+    c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
+    if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
+    if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) c->staged_words = (uint64_t)v; }
+    for (auto& sl : c->slot) {
+        LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
+        LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+        LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, sizeof(uint32_t)));
+        LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, sizeof(unsigned long long)));
+    }
     return LZANI_OK;
 }
 
@@ -169,6 +238,13 @@ extern "C" void lzani_destroy(lzani_ctx* c)
         cudaFree(c->d_regs); cudaFree(c->d_reg_counter);
         cudaFree(c->d_flags); cudaFree(c->d_blk_cnt); cudaFree(c->d_blk_off); cudaFree(c->d_loc);
         cudaFree(c->d_eff_len); cudaFree(c->d_pairs);
+        for (auto& sl : c->slot) {
+            free_slot(sl);
+            cudaFree(sl.B.counter);
+            if (sl.h_total) cudaFreeHost(sl.h_total);
+            if (sl.done) cudaEventDestroy(sl.done);
+            if (sl.st) cudaStreamDestroy(sl.st);
+        }
         for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
         if (c->stream) cudaStreamDestroy(c->stream);
     }
@@ -375,6 +451,36 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         LZ_CUDA(c, cudaMemsetAsync(c->d_reg_counter, 0, sizeof(unsigned long long), c->stream));
     }
 
+    // ---- staged parse: words (32 query positions) per sequence as a query, chunk scratch.  Allocated
+    // before the index budget is taken from what is left.
+    std::vector<uint32_t> wq;
+    uint64_t words_all = 0, words_run = 0;
+    uint32_t words_max = 0;
+    bool staged = !rq && c->staged != 0 && n_pairs > 0;
+    if (staged) {
+        wq.resize(n);
+        for (uint32_t i = 0; i < n; ++i) {
+            const int64_t n_loop = (int64_t)c->meta[i].len + P.mrd - P.msl;
+            if ((int64_t)c->meta[i].len + P.mrd >= (int64_t)LZ_STAGED_MAX_POS) staged = false;   // hit-list entries hold 29-bit positions
+            wq[i] = n_loop > 0 ? (uint32_t)((n_loop + 31) / 32) : 0u;
+            words_all += wq[i];
+            words_max = std::max(words_max, wq[i]);
+        }
+    }
+    if (staged) {
+        if (q_ids) for (uint64_t k = 0; k < n_pairs; ++k) words_run += wq[q_src[k]];
+        else for (uint32_t j = 0; j < n_rows; ++j) words_run += words_all - wq[row_ref[j]];
+        const uint64_t wcap = std::max<uint64_t>(std::min<uint64_t>(c->staged_words, words_run), std::max<uint32_t>(words_max, 1u));
+        const uint64_t pcap = std::min<uint64_t>(n_pairs, (uint64_t)1 << 19);
+        const uint64_t rcap = wcap + wcap / 4 + 1024;
+        const int n_slots = words_run > wcap ? 2 : 1;
+        for (int i = 0; i < n_slots; ++i) {
+            lzani_ctx::Slot& sl = c->slot[i];
+            if (pcap > sl.pairs_cap || wcap > sl.words_cap || rcap > sl.recs_cap)
+                if (int rc = ensure_slot(c, sl, std::max(pcap, sl.pairs_cap), std::max(wcap, sl.words_cap), std::max(rcap, sl.recs_cap))) return rc;
+        }
+    }
+
     // ---- batches of consecutive rows under the index budget
     uint64_t budget = c->budget;
     if (!budget) {
@@ -407,6 +513,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
 
     lzani_timing_t T{};
     T.n_batches = (uint32_t)batches.size();
+    c->staged_chunks = 0;
     cudaStream_t st = c->stream;
 
     // ---- H2D: the pair list
@@ -452,7 +559,95 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                                                 c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a],
                                                 row_off[b.b], P, c->d_bitmap, c->d_table, c->d_counter, c->d_out,
                                                 c->d_regs, c->d_reg_counter, rq->cap));
-            else
+            else if (staged) {
+                // ---- chunks of consecutive pairs through the staged pipeline, alternating between the two slots
+                const uint64_t kb = row_off[b.a], ke = row_off[b.b];
+                for (auto& sl : c->slot) LZ_CUDA(c, cudaStreamWaitEvent(sl.st, c->ev[4], 0));
+                const int wgrid = c->n_sm * c->walk_blocks_per_sm;
+                auto pair_q = [&](uint32_t j, uint64_t k) -> uint32_t {
+                    if (q_ids) return q_src[k];
+                    uint32_t q = (uint32_t)(k - row_off[j]);
+                    if (q >= row_ref[j]) ++q;
+                    return q;
+                };
+                auto range_words = [&](uint64_t k0, uint64_t k1) -> uint64_t {
+                    uint64_t wsum = 0;
+                    uint32_t j = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), k0) - row_off.begin()) - 1;
+                    for (uint64_t k = k0; k < k1; ++k) {
+                        while (row_off[j + 1] <= k) ++j;
+                        wsum += wq[pair_q(j, k)];
+                    }
+                    return wsum;
+                };
+                struct Range { uint64_t k0, k1, words; };
+                std::vector<Range> redo;             // halves of a chunk whose records did not fit
+                uint64_t k_next = kb;
+                uint32_t j_cur = b.a;
+                while (k_next < ke || !redo.empty()) {
+                    Range ch{0, 0, 0};
+                    lzani_ctx::Slot& sl = c->slot[c->staged_chunks & 1u];
+                    if (!redo.empty()) { ch = redo.back(); redo.pop_back(); }
+                    else {
+                        // the next chunk: as many pairs as the word / record / pair capacities allow
+                        uint64_t w_target = c->staged_words;
+                        const uint64_t have_r = sl.recs_cap ? sl.recs_cap : c->slot[0].recs_cap;
+                        const uint64_t by_recs = (uint64_t)((double)have_r / (1.15 * c->rec_per_word));
+                        if (by_recs < w_target) w_target = by_recs;
+                        const uint64_t p_max = (uint64_t)1 << 19;
+                        uint64_t k = k_next, wsum = 0;
+                        while (k < ke && k - k_next < p_max) {
+                            while (row_off[j_cur + 1] <= k) ++j_cur;
+                            if (!q_ids && k == row_off[j_cur]) {          // a whole dense row at once
+                                const uint64_t rw = words_all - wq[row_ref[j_cur]], np = row_off[j_cur + 1] - k;
+                                if (wsum + rw <= w_target && k - k_next + np <= p_max) { wsum += rw; k += np; continue; }
+                            }
+                            const uint32_t w1 = wq[pair_q(j_cur, k)];
+                            if (k > k_next && wsum + w1 > w_target) break;
+                            wsum += w1;
+                            ++k;
+                        }
+                        ch = Range{k_next, k, wsum};
+                        k_next = k;
+                    }
+                    const uint64_t np = ch.k1 - ch.k0;
+                    if (np > sl.pairs_cap || ch.words > sl.words_cap || !sl.recs_cap) {
+                        LZ_CUDA(c, cudaStreamSynchronize(sl.st));
+                        if (int rc = ensure_slot(c, sl, std::max(np, std::max(sl.pairs_cap, c->slot[0].pairs_cap)),
+                                                 std::max(ch.words, std::max(sl.words_cap, c->slot[0].words_cap)),
+                                                 std::max(sl.recs_cap, c->slot[0].recs_cap))) return rc;
+                    }
+                    LZ_CUDA(c, launch_staged_scan(sl.st, sl.B, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
+                                                  c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, ch.k0, (uint32_t)np,
+                                                  ch.words, P, c->d_bitmap, c->n_sm));
+                    LZ_CUDA(c, cudaMemcpyAsync(sl.h_total, sl.B.rec_off + ch.words, sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.st));
+                    LZ_CUDA(c, cudaStreamSynchronize(sl.st));
+                    const uint64_t n_hit = *sl.h_total;
+                    T.launches += 2;
+                    if (ch.words) {
+                        const double ratio = (double)n_hit / (double)ch.words;
+                        c->rec_per_word = ratio > c->rec_per_word ? ratio : 0.5 * (c->rec_per_word + ratio);
+                        if (c->rec_per_word < 0.25) c->rec_per_word = 0.25;
+                    }
+                    if (n_hit > sl.recs_cap) {
+                        if (np > 1) {                      // too many hit runs for the record buffers: halve the chunk
+                            const uint64_t mid = ch.k0 + np / 2;
+                            const uint64_t w0 = range_words(ch.k0, mid);
+                            redo.push_back(Range{mid, ch.k1, ch.words - w0});
+                            redo.push_back(Range{ch.k0, mid, w0});
+                            continue;
+                        }
+                        if (int rc = ensure_slot(c, sl, sl.pairs_cap, sl.words_cap, n_hit)) return rc;
+                    }
+                    LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
+                                                  c->d_bitmap, c->d_table, c->d_out));
+                    T.launches += 3;
+                    ++c->staged_chunks;
+                }
+                for (auto& sl : c->slot) {
+                    LZ_CUDA(c, cudaEventRecord(sl.done, sl.st));
+                    LZ_CUDA(c, cudaStreamWaitEvent(st, sl.done, 0));
+                }
+            } else
                 LZ_CUDA(c, launch_parse(st, grid, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
                                         c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, row_off[b.a], row_off[b.b], P,
                                         c->d_bitmap, c->d_table, c->d_counter, c->d_out));
@@ -461,7 +656,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
             T.h2d_ms += ms_between(c->ev[2], c->ev[3]);
             T.index_ms += ms_between(c->ev[3], c->ev[4]);
             T.parse_ms += ms_between(c->ev[4], c->ev[5]);
-            T.launches += (h_blk[nb] ? 1 : 0) + (row_off[b.b] > row_off[b.a] ? 1 : 0);
+            T.launches += (h_blk[nb] ? 1 : 0) + (!staged && row_off[b.b] > row_off[b.a] ? 1 : 0);
         }
     }
     LZ_CUDA(c, cudaEventRecord(c->ev[6], st));

@@ -9,6 +9,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cub/cub.cuh>
+#include <thrust/iterator/transform_iterator.h>
+
 #include "kernels.h"
 #include "parse_core.h"
 
@@ -121,6 +124,193 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
         pv.tbits = ix.tbits;
         const PairResult res = parse_pair(w, pv, P, sc);
         if (w.lane == 0) out[k] = make_int3(res.m, res.x, res.n);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3 staged.  The parse of a CHUNK of consecutive pairs as a pipeline of plain kernels (parse_core.h,
+// "staged pipeline"): what depends on the query position alone is computed for all pairs of the chunk
+// by data-parallel kernels at full occupancy and stored; only the sequential walk stays warp-per-pair.
+//
+//   S0 k_pair_desc     thread per pair        pair descriptor + number of 32-position words of its loop
+//      (exclusive scan -> word_off)
+//   S1 k_scan_hits     thread per word        hit mask of 32 query positions (anchor presence bitmap)
+//      (exclusive scan of the run counts -> rec_off)
+//   S2 k_expand_hits   thread per word        hit list: (pair, position, run length) per hit run
+//   S3 k_hit_records   thread per hit run     table probe, match length, both approximate extensions,
+//                                             speculative seed scan -> one 16-byte record
+//   S4 k_walk_pairs    warp per pair          the state machine of parser.cpp:501-708 over the records
+template <class PT>
+__global__ void __launch_bounds__(256)
+k_pair_desc(const SeqMeta* __restrict__ meta, const uint32_t* __restrict__ row_ref,
+            const RefIndex* __restrict__ row_idx, const uint64_t* __restrict__ row_off, uint32_t n_rows,
+            const uint32_t* __restrict__ q_ids, uint64_t pair_begin, uint32_t n_pairs, PT P,
+            PairDesc* __restrict__ desc, uint32_t* __restrict__ n_words)
+{
+    const uint32_t pl = blockIdx.x * 256u + threadIdx.x;
+    if (pl > n_pairs) return;
+    if (pl == n_pairs) { n_words[pl] = 0; return; }
+    const uint64_t k = pair_begin + pl;
+    const uint32_t j = find_segment<uint64_t>(row_off, n_rows, k);
+    const uint32_t r = row_ref[j];
+    uint32_t q;
+    if (q_ids) q = q_ids[k];
+    else {
+        q = (uint32_t)(k - row_off[j]);
+        if (q >= r) ++q;
+    }
+    const SeqMeta mr = meta[r], mq = meta[q];
+    const RefIndex ix = row_idx[j];
+    PairDesc d;
+    d.q_rec = mq.q_rec; d.r_rec = mr.r_rec;
+    d.bitmap_word = ix.bitmap_word; d.table_slot = ix.table_slot;
+    d.Dq = (int)mq.len + P.mrd;
+    d.Dr = r_form_len((int)mr.len, P.mrd);
+    d.bbits = ix.bbits; d.tbits = ix.tbits;
+    desc[pl] = d;
+    const int n_loop = d.Dq - P.msl;
+    n_words[pl] = n_loop > 0 ? (uint32_t)((n_loop + 31) / 32) : 0u;
+}
+
+__device__ __forceinline__ PairView view_of(const PairDesc& d, const Rec* recs, const uint32_t* bitmap_pool,
+                                            const uint64_t* table_pool)
+{
+    PairView pv;
+    pv.q = recs + d.q_rec; pv.Dq = d.Dq;
+    pv.r = recs + d.r_rec; pv.Dr = d.Dr;
+    pv.bitmap = bitmap_pool + d.bitmap_word; pv.bbits = d.bbits;
+    pv.table = table_pool + d.table_slot; pv.tbits = d.tbits;
+    return pv;
+}
+
+// S1.  Persistent blocks of LZ_SCAN_THREADS threads, one per SM, each over a contiguous range of tiles of
+// LZ_SCAN_TILE words.  The anchor presence bitmap of the reference is random-accessed once per query
+// position -- 32-byte L2 sectors for 1 bit -- so the block keeps a folded copy (<= 128 KiB, coarse_fold_word)
+// in shared memory and only the positions that pass it touch the exact bitmap.  Consecutive pairs of a
+// chunk share their reference (CSR order), so the copy is re-folded only when the reference changes.
+constexpr int LZ_SCAN_THREADS = 1024;
+constexpr uint32_t LZ_SCAN_TILE = 8192;
+template <class PT>
+__global__ void __launch_bounds__(LZ_SCAN_THREADS, 1)
+k_scan_hits(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off,
+            uint32_t n_pairs, PT P, const uint32_t* __restrict__ bitmap_pool, uint32_t* __restrict__ hm,
+            uint32_t* __restrict__ wpair)
+{
+    extern __shared__ uint32_t coarse[];
+    __shared__ uint32_t s_pl, s_end;
+    const uint32_t n_words = word_off[n_pairs];
+    const uint32_t n_tiles = (n_words + LZ_SCAN_TILE - 1) / LZ_SCAN_TILE;
+    const uint32_t t0 = (uint32_t)((uint64_t)n_tiles * blockIdx.x / gridDim.x);
+    const uint32_t t1 = (uint32_t)((uint64_t)n_tiles * (blockIdx.x + 1) / gridDim.x);
+    unsigned long long have = ~0ull;          // bitmap whose folded copy is in shared memory
+    for (uint32_t tile = t0; tile < t1; ++tile) {
+        const uint32_t wb = tile * LZ_SCAN_TILE;
+        const uint32_t we = wb + LZ_SCAN_TILE < n_words ? wb + LZ_SCAN_TILE : n_words;
+        uint32_t w = wb;
+        while (w < we) {
+            // segment: the words of consecutive pairs with the same reference, inside the tile
+            if (threadIdx.x == 0) {
+                uint32_t pl = find_segment<uint32_t>(word_off, n_pairs, w);
+                const unsigned long long bm = desc[pl].bitmap_word;
+                uint32_t e = pl;
+                while (e + 1 < n_pairs && word_off[e + 1] < we && desc[e + 1].bitmap_word == bm) ++e;
+                s_pl = pl;
+                s_end = word_off[e + 1] < we ? word_off[e + 1] : we;
+            }
+            __syncthreads();
+            const uint32_t pl0 = s_pl, seg_end = s_end;
+            const PairDesc d0 = desc[pl0];
+            if (d0.bitmap_word != have) {
+                const uint32_t cw = coarse_words(d0.bbits);
+                for (uint32_t c = threadIdx.x; c < cw; c += LZ_SCAN_THREADS)
+                    coarse[c] = coarse_fold_word(bitmap_pool + d0.bitmap_word, d0.bbits, c);
+                have = d0.bitmap_word;
+                __syncthreads();
+            }
+            uint32_t pl = pl0;
+            for (uint32_t gw = w + threadIdx.x; gw < seg_end; gw += LZ_SCAN_THREADS) {
+                while (gw >= word_off[pl + 1]) ++pl;
+                const PairDesc d = desc[pl];
+                const PairView pv = view_of(d, recs, bitmap_pool, nullptr);
+                hm[gw] = scan_word_coarse(pv, P, (int)(32u * (gw - word_off[pl])), d.Dq - P.msl, coarse);
+                wpair[gw] = pl;
+            }
+            w = seg_end;
+            __syncthreads();
+        }
+    }
+}
+
+// input of the second scan: hit runs per word
+struct RunCount {
+    __host__ __device__ __forceinline__ uint32_t operator()(uint32_t m) const { return (uint32_t)__builtin_popcount(run_first_bits(m)); }
+};
+
+__global__ void __launch_bounds__(256)
+k_expand_hits(const uint32_t* __restrict__ hm, const uint32_t* __restrict__ wpair, const uint32_t* __restrict__ word_off,
+              uint32_t n_words, const uint32_t* __restrict__ rec_off, HitEntry* __restrict__ list)
+{
+    const uint32_t gw = blockIdx.x * 256u + threadIdx.x;
+    if (gw >= n_words) return;
+    const uint32_t m = hm[gw];
+    if (!m) return;
+    const uint32_t pl = wpair[gw];
+    const uint32_t pos0 = 32u * (gw - word_off[pl]);
+    uint32_t at = rec_off[gw];
+    uint32_t f = run_first_bits(m);
+    while (f) {
+        const int b = ctz32(f);
+        f &= f - 1u;
+        HitEntry e;
+        e.pair = pl;
+        e.pr = (pos0 + (uint32_t)b) | ((uint32_t)run_following(m, b) << HIT_ENTRY_RUN_SHIFT);
+        list[at++] = e;
+    }
+}
+
+struct WarpSyncFn {
+    __device__ __forceinline__ void operator()() const { __syncwarp(); }
+};
+
+template <class PT>
+__global__ void __launch_bounds__(LZ_RECORD_THREADS)
+k_hit_records(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
+              const uint32_t* __restrict__ rec_total, PT P, const uint32_t* __restrict__ bitmap_pool,
+              const uint64_t* __restrict__ table_pool, Rec* __restrict__ out)
+{
+    const uint32_t total = *rec_total;
+    const uint32_t t = blockIdx.x * (uint32_t)LZ_RECORD_THREADS + threadIdx.x;
+    const bool live = t < total;
+    PairView pv{};
+    int n_loop = 0;
+    if (live) {
+        const PairDesc d = desc[list[t].pair];
+        pv = view_of(d, recs, bitmap_pool, table_pool);
+        n_loop = d.Dq - P.msl;
+    }
+    const Rec o = hit_record(pv, P, n_loop, list, (uint64_t)t, (uint64_t)total, live, WarpSyncFn{});
+    if (live) reinterpret_cast<uint4*>(out)[t] = make_uint4(o.x, o.y, o.z, o.w);
+}
+
+template <class PT>
+__global__ void __launch_bounds__(LZ_WALK_THREADS, LZ_WALK_MIN_BLOCKS)
+k_walk_pairs(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off,
+             const uint32_t* __restrict__ rec_off, const Rec* __restrict__ hit_recs, uint32_t n_pairs,
+             uint64_t pair_begin, PT P, const uint32_t* __restrict__ bitmap_pool,
+             const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
+             int3* __restrict__ out)
+{
+    DevWarp w((int)(threadIdx.x & 31u));
+    for (;;) {
+        unsigned long long k = 0;
+        if (w.lane == 0) k = atomicAdd(counter, 1ull);
+        k = __shfl_sync(0xFFFFFFFFu, k, 0);
+        if (k >= n_pairs) return;
+        const uint32_t pl = (uint32_t)k;
+        const PairView pv = view_of(desc[pl], recs, bitmap_pool, table_pool);
+        const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
+        const PairResult res = walk_pair(w, pv, P, hit_recs + r0, r1 - r0);
+        if (w.lane == 0) out[pair_begin + pl] = make_int3(res.m, res.x, res.n);
     }
 }
 
@@ -257,6 +447,94 @@ cudaError_t launch_parse_regions(cudaStream_t st, int grid_blocks, const Rec* re
             recs, meta, row_ref, row_idx, row_off, n_rows, q_ids, pair_begin, pair_end, P, bitmap_pool, table_pool, counter,
             reinterpret_cast<int3*>(out), regs, reg_counter, (unsigned long long)reg_cap);
     return cudaGetLastError();
+}
+
+
+// ---- staged pipeline launches.  PT dispatch as launch_parse(): compile-time defaults or run-time values.
+template <class F>
+static cudaError_t with_prm(const Prm& P, F f)
+{
+    if (is_default_kernel_params(P)) return f(PrmDefault{P.mrd, P.mqd, P.reg});
+    return f(P);
+}
+
+int walk_blocks_per_sm(const Prm& P)
+{
+    int nb = 0;
+    const cudaError_t e = is_default_kernel_params(P)
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_pairs<PrmDefault>, LZ_WALK_THREADS, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_pairs<Prm>, LZ_WALK_THREADS, 0);
+    if (e != cudaSuccess || nb < 1) nb = 1;
+    return nb;
+}
+
+size_t staged_scan_bytes(uint64_t n_items)
+{
+    size_t a = 0, b = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n_items);
+    auto it = thrust::make_transform_iterator((const uint32_t*)nullptr, RunCount{});
+    cub::DeviceScan::ExclusiveSum(nullptr, b, it, (uint32_t*)nullptr, (int64_t)n_items);
+    return a > b ? a : b;
+}
+
+cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
+                               const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,
+                               uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint32_t n_pairs,
+                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks)
+{
+    cudaError_t e = with_prm(P, [&](auto PT) {
+        k_pair_desc<<<n_pairs / 256 + 1, 256, 0, st>>>(meta, row_ref, row_idx, row_off, n_rows, q_ids, pair_begin, n_pairs,
+                                                         PT, B.desc, B.n_words);
+        return cudaGetLastError();
+    });
+    if (e != cudaSuccess) return e;
+    size_t tb = B.tmp_bytes;
+    e = cub::DeviceScan::ExclusiveSum(B.tmp, tb, (const uint32_t*)B.n_words, B.word_off, (int64_t)n_pairs + 1, st);
+    if (e != cudaSuccess) return e;
+    if (n_words) {
+        e = with_prm(P, [&](auto PT) {
+            using K = decltype(PT);
+            static bool attr_set = false;      // per instantiation
+            const size_t smem = sizeof(uint32_t) << (LZ_COARSE_BITS - 5);
+            if (!attr_set) {
+                cudaError_t ea = cudaFuncSetAttribute(k_scan_hits<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (ea != cudaSuccess) return ea;
+                attr_set = true;
+            }
+            k_scan_hits<K><<<scan_blocks, LZ_SCAN_THREADS, smem, st>>>(recs, B.desc, B.word_off, n_pairs, PT, bitmap_pool, B.hm, B.wpair);
+            return cudaGetLastError();
+        });
+        if (e != cudaSuccess) return e;
+    }
+    auto it = thrust::make_transform_iterator((const uint32_t*)B.hm, RunCount{});
+    tb = B.tmp_bytes;
+    return cub::DeviceScan::ExclusiveSum(B.tmp, tb, it, B.rec_off, (int64_t)n_words + 1, st);
+}
+
+cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
+                               uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,
+                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out)
+{
+    if (n_words) {
+        k_expand_hits<<<(unsigned)((n_words + 255) / 256), 256, 0, st>>>(B.hm, B.wpair, B.word_off, (uint32_t)n_words, B.rec_off, B.list);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (n_recs) {
+        cudaError_t e = with_prm(P, [&](auto PT) {
+            k_hit_records<<<(unsigned)((n_recs + LZ_RECORD_THREADS - 1) / LZ_RECORD_THREADS), LZ_RECORD_THREADS, 0, st>>>(
+                recs, B.desc, B.list, B.rec_off + n_words, PT, bitmap_pool, table_pool, B.recs);
+            return cudaGetLastError();
+        });
+        if (e != cudaSuccess) return e;
+    }
+    cudaError_t e = cudaMemsetAsync(B.counter, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    return with_prm(P, [&](auto PT) {
+        k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
+                                                            PT, bitmap_pool, table_pool, B.counter, reinterpret_cast<int3*>(out));
+        return cudaGetLastError();
+    });
 }
 
 }  // namespace lzani

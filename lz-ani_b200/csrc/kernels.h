@@ -14,6 +14,16 @@
 #define LZ_PARSE_MIN_BLOCKS 5
 #endif
 
+#ifndef LZ_WALK_THREADS
+#define LZ_WALK_THREADS 128
+#endif
+#ifndef LZ_WALK_MIN_BLOCKS
+#define LZ_WALK_MIN_BLOCKS 5
+#endif
+#ifndef LZ_RECORD_THREADS
+#define LZ_RECORD_THREADS 128
+#endif
+
 namespace lzani {
 
 cudaError_t launch_pack(cudaStream_t st, const uint8_t* src, const SeqMeta* meta, const uint64_t* rec_base,
@@ -40,6 +50,37 @@ cudaError_t launch_parse(cudaStream_t st, int grid_blocks, const Rec* recs, cons
                          uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint64_t pair_end,
                          const Prm& P, const uint32_t* bitmap_pool, const uint64_t* table_pool,
                          unsigned long long* counter, void* out);
+
+// ---- staged pipeline (kernels.cu "K3 staged"): per-chunk scratch and launches
+struct PairDesc {                 // everything the stage kernels need to know about one pair of the chunk
+    uint64_t q_rec, r_rec;        // first records of the query's Q-form / the reference's R-form
+    uint64_t bitmap_word, table_slot;
+    int Dq, Dr;
+    uint32_t bbits, tbits;
+};
+struct StagedBufs {
+    PairDesc* desc;               // [pairs]
+    uint32_t* n_words;            // [pairs + 1]
+    uint32_t* word_off;           // [pairs + 1]  first word of each pair
+    uint32_t* hm;                 // [words + 1]  hit masks
+    uint32_t* wpair;              // [words]      pair of each word
+    uint32_t* rec_off;            // [words + 1]  first record of each word; [words] = records of the chunk
+    HitEntry* list;               // [records]
+    Rec* recs;                    // [records]
+    void* tmp; size_t tmp_bytes;  // CUB scan scratch
+    unsigned long long* counter;
+};
+int walk_blocks_per_sm(const Prm& P);
+size_t staged_scan_bytes(uint64_t n_items);
+// S0, scan, S1, scan: afterwards rec_off[n_words] holds the number of records of the chunk
+cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
+                               const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,
+                               uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint32_t n_pairs,
+                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks);
+// S2, S3, S4
+cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
+                               uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,
+                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out);
 
 // ---- postproc.cu: pairing of the two directions, derived metrics, --out-filter compaction
 // where the results of reference row r live (this GPU or a peer): res[i] is the result of the i-th

@@ -70,6 +70,11 @@ struct RefIndex {
     uint32_t tbits;        // log2(table slots)
 };
 
+// staged parse: one element of a chunk's hit list (a run of consecutive anchor-bitmap hits of one pair)
+struct HitEntry { uint32_t pair, pr; };          // pair (chunk-relative), position | run length << 29
+constexpr int HIT_ENTRY_RUN_SHIFT = 29;
+constexpr int LZ_STAGED_MAX_POS = 1 << HIT_ENTRY_RUN_SHIFT;
+
 LZ_HD int q_form_recs(int len, int mrd) { return (len + mrd + 31) / 32 + LZ_PAD_RECS; }
 LZ_HD int r_form_len(int len, int mrd) { return 2 * len + 3 * mrd; }
 LZ_HD int r_form_recs(int len, int mrd) { return (r_form_len(len, mrd) + 31) / 32 + LZ_PAD_RECS; }

@@ -977,6 +977,168 @@ LZ_HD Event next_event(W& w, const LI& r_p, const LU& r_pos, const LU& r_w2, con
     return o;
 }
 
+// ---- hit mask of the 32 query positions starting at pos0 (a multiple of 32): bit t is set iff the
+// mal-mer at pos0+t has no N and its bit in the reference's anchor presence bitmap is set -- i.e. the
+// probe chain of ht_long (parser.cpp:516-518) would not end at once.  Positions >= end are cleared.
+template <class PT>
+LZ_HD uint32_t scan_word(const PairView& pv, const PT& P, int pos0, int end)
+{
+    uint32_t m = 0;
+    if (pos0 < end) {
+        const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
+        // positions whose mal-mer covers an N (rare: one test per 32 positions)
+        uint32_t bad = 0;
+        if (a.z | b.z) {
+            const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
+            uint64_t u = nz;
+            for (int j = 1; j < P.mal; ++j) u |= nz >> j;
+            bad = (uint32_t)u;
+        }
+#if defined(__CUDA_ARCH__)
+#pragma unroll kScanUnroll
+#endif
+        for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
+            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+            const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
+            const uint32_t bw = ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u);
+            m = (m >> 1) | (bw << 31);      // bit of position t ends up at bit t
+        }
+        m &= ~bad;
+        const int nv = end - pos0;
+        if (nv < 32) m &= low_mask32(nv);
+    }
+    return m;
+}
+// ---- the same hit mask through a two-level bitmap: `coarse` (shared memory in k_scan_hits) is the
+// reference's presence bitmap OR-folded down to at most 2^LZ_COARSE_BITS bits; only positions that pass it
+// (about 4x the true hit rate for the default parameters) look at the exact bitmap in L2.
+constexpr int LZ_COARSE_BITS = 20;                       // 128 KiB
+LZ_HD uint32_t coarse_words(uint32_t bbits) { return bbits >= (uint32_t)LZ_COARSE_BITS ? (1u << (LZ_COARSE_BITS - 5)) : (bbits > 5 ? (1u << (bbits - 5)) : 1u); }
+// word c of the folded bitmap: the OR of the exact words c, c + Cw, c + 2 Cw, ...
+LZ_HD uint32_t coarse_fold_word(const uint32_t* bitmap, uint32_t bbits, uint32_t c)
+{
+    const uint32_t cw = coarse_words(bbits);
+    const uint32_t ew = bbits > 5 ? (1u << (bbits - 5)) : 1u;
+    uint32_t v = 0;
+    for (uint32_t t = c; t < ew; t += cw) v |= ld_u32(bitmap + t);
+    return v;
+}
+template <class PT>
+LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int end, const uint32_t* coarse)
+{
+    uint32_t m = 0;
+    if (pos0 < end) {
+        const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
+        uint32_t bad = 0;
+        if (a.z | b.z) {
+            const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
+            uint64_t u = nz;
+            for (int j = 1; j < P.mal; ++j) u |= nz >> j;
+            bad = (uint32_t)u;
+        }
+        const uint32_t cbits = pv.bbits < (uint32_t)LZ_COARSE_BITS ? pv.bbits : (uint32_t)LZ_COARSE_BITS;
+        const uint32_t cmask = (1u << cbits) - 1u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
+#endif
+        for (int t = 0; t < 32; ++t) {
+            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+            const uint32_t ci = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits) & cmask;
+            const uint32_t bw = coarse[ci >> 5] >> (ci & 31u);
+            m = (m >> 1) | (bw << 31);
+        }
+        m &= ~bad;
+        const int nv = end - pos0;
+        if (nv < 32) m &= low_mask32(nv);
+        if (pv.bbits > (uint32_t)LZ_COARSE_BITS) {
+            uint32_t t = m;
+            while (t) {                     // the exact bitmap decides
+                const int j = ctz32(t);
+                t &= t - 1u;
+                const uint32_t lo = funnel_r(a.x, b.x, j), hi = funnel_r(a.y, b.y, j);
+                const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
+                if (!((ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u)) & 1u)) m &= ~(1u << j);
+            }
+        }
+    }
+    return m;
+}
+// first positions of the runs of consecutive hits inside a hit mask (a run never crosses a multiple of 8)
+LZ_HD uint32_t run_first_bits(uint32_t m) { return m & ~(m & (m << 1) & ~0x01010101u); }
+
+// ---- staged pipeline (kernels.cu: k_scan_hits -> k_expand_hits -> k_hit_records -> k_walk_pairs).
+// Everything a hit record holds depends on the query position alone, never on the parse state, so the
+// records of ALL hits of a chunk of pairs are computed by plain data-parallel kernels (one thread per
+// 32 query positions, then one thread per hit run) and stored in HBM in position order; the walk kernel
+// then only loads them, 32 at a time.  A stored record is one Rec: x = query position, y = reference
+// position of the best anchor, z = w2, w = w3 (the fields of hit_probe / hit_extend / spec_first_seed).
+// (HitEntry, the hit-list element, is declared in layout.h.)
+
+// Stage C of a record: the speculative seed scan of the window the hit opens if it is taken
+// (spec_first_seed), over query positions up to lim_p (the next hit run, or the last loop position)
+template <class PT>
+LZ_HD void hit_spec(const PairView& pv, const PT& P, int p, int lim_p, uint32_t pos, uint32_t& w2, uint32_t& w3)
+{
+    const int adv = (int)(w2 & 63u) + (int)((w2 >> 6) & 63u);
+    const int si0 = p + adv, sP0 = (int)pos + adv;
+    int K = lim_p - si0;
+    if (K > P.mqd) K = P.mqd;
+    const int ks = spec_first_seed(pv, P, si0, sP0, K);
+    if (ks >= 0) {
+        w3 |= ((uint32_t)(K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
+        w2 |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;
+    }
+}
+
+// length of the run of hits that follow the run-first bit b of hit mask m (0..7)
+LZ_HD int run_following(uint32_t m, int b)
+{
+    const uint32_t sec = m & (m << 1) & ~0x01010101u;
+    const uint32_t follow = b < 31 ? ~(sec >> (b + 1)) : 1u;     // run: sec bits right behind b
+    return ctz32(follow);
+}
+
+// The stored record of hit-list entry t (one thread per entry in k_hit_records).  `sync` is the
+// reconvergence point between the stages (lanes take different numbers of probe / scan iterations).
+template <class PT, class SyncFn>
+LZ_HD Rec hit_record(const PairView& pv, const PT& P, int n_loop, const HitEntry* list, uint64_t t, uint64_t total,
+                     bool live, SyncFn sync)
+{
+    Rec o; o.x = 0; o.y = 0; o.z = 0; o.w = 0;
+    HitEntry e; e.pair = 0; e.pr = 0;
+    if (live) e = list[t];
+    const int p = (int)(e.pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
+    uint32_t pos = 0, w2 = 0, w3 = 0;
+    if (live) hit_probe(pv, P, p, pos, w2);
+    w2 |= (e.pr >> HIT_ENTRY_RUN_SHIFT) << HIT_RUN_SHIFT;
+    sync();
+    if (live && (w2 & (HIT_LIVE | HIT_DEFER)) == HIT_LIVE) hit_extend(pv, P, p, (int)pos, w2, w3);
+    sync();
+    if (PT::kSpecSeeds && P.mqd <= SPEC_MAX_K && live && (w2 & HIT_FWD)) {
+        // scanned up to the next hit run of this pair at or after the window's start (inclusive), or the
+        // last position of the loop
+        const int si0 = p + (int)(w2 & 63u) + (int)((w2 >> 6) & 63u);
+        int lim_p = n_loop - 1;
+        for (uint64_t u = t + 1; u < total && list[u].pair == e.pair; ++u) {
+            const int pu = (int)(list[u].pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
+            if (pu >= si0) { lim_p = pu; break; }
+        }
+        hit_spec(pv, P, p, lim_p, pos, w2, w3);
+    }
+    o.x = (uint32_t)p; o.y = pos; o.z = w2; o.w = w3;
+    return o;
+}
+
+// where parse_pair() gets its batches of hit records from
+struct InlineBatches {                   // built by the warp itself, window by window (one-kernel path, regions kernel)
+    static constexpr bool kStored = false;
+    const Rec* recs = nullptr; uint32_t n = 0;
+};
+struct StoredBatches {                   // loaded from the records the staged kernels wrote
+    static constexpr bool kStored = true;
+    const Rec* recs; uint32_t n;         // this pair's records, position order
+};
+
 // ---- the whole pair.
 //
 // Three nested granularities:
@@ -990,10 +1152,10 @@ LZ_HD Event next_event(W& w, const LI& r_p, const LU& r_pos, const LU& r_w2, con
 //          from hit to hit; with one (the mqd positions after a match) it also looks for seeds
 //          along the diagonals of the prediction window.
 // `list` is 32 uint16 of per-warp scratch (shared memory on the device).
-template <class W, class PT, class RS>
-LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc, RS& rt)
+template <class W, class PT, class RS, class BS>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc, RS& rt, const BS& bs)
 {
-    uint16_t* list = sc->list;
+    uint16_t* list = BS::kStored ? nullptr : sc->list;
     if (RS::kActive) rt.clear_all();
     ParseState s;
     s.i = 0; s.pred = -1; s.lit = 0;
@@ -1012,9 +1174,11 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
     typename W::template Lanes<uint32_t> r_pos, r_w2, r_w3;
     typename W::template Lanes<int> r_p, r_nx;     // r_nx: successor links (see "successor links" below)
+    uint32_t cur = 0;                  // stored batches: first record of the current batch
+    int b_loaded = 0;                  //                 and how many records it holds
     LZ_EACH(w, ln)
     {
-        for (int q = 0; q < LZ_WIN_WORDS; ++q) sc->hm[q][ln] = 0;
+        if (!BS::kStored) for (int q = 0; q < LZ_WIN_WORDS; ++q) sc->hm[q][ln] = 0;
         r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; r_nx[ln] = 32;
     }
 
@@ -1027,6 +1191,49 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         int m_j = -1;                  // batch record the match was taken from (when m_w2 != 0)
         if (i0 >= b_cover) {
             if (i0 >= n_loop) break;       // b_cover <= n_loop: the end of the loop (:501) is only met here
+            if (BS::kStored) {
+                // ---- next batch: the first <= 32 stored records not entirely behind the walk.  The records
+                // are in position order and runs do not overlap, so "behind" is a prefix property.
+                cur += (uint32_t)b_loaded;             // b_cover <= i0: the whole previous batch lies behind
+                for (;;) {
+                    typename W::template Lanes<int> behind;
+                    LZ_EACH(w, ln)
+                    {
+                        const uint32_t idx = cur + (uint32_t)ln;
+                        Rec h; h.x = 0x7FFFFFFFu; h.y = 0; h.z = 0; h.w = 0;
+                        if (idx < bs.n) h = ld_rec(bs.recs + idx);
+                        r_p[ln] = (int)h.x; r_pos[ln] = h.y; r_w2[ln] = h.z; r_w3[ln] = h.w;
+                        behind[ln] = idx < bs.n && (int)h.x + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
+                    }
+                    const int nb = popc32(w.ballot(behind));
+                    if (!nb) break;
+                    cur += (uint32_t)nb;
+                    if (nb == 32) {
+                        // a long match jumped far ahead: gallop over blocks of 32 records
+                        for (;;) {
+                            typename W::template Lanes<int> far;
+                            LZ_EACH(w, ln)
+                            {
+                                const uint64_t idx = (uint64_t)cur + 32u * (uint32_t)ln + 31u;
+                                far[ln] = 0;
+                                if (idx < bs.n) {
+                                    const Rec h = ld_rec(bs.recs + idx);
+                                    far[ln] = (int)h.x + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
+                                }
+                            }
+                            const int nf = popc32(w.ballot(far));
+                            cur += 32u * (uint32_t)nf;
+                            if (nf < 32) break;
+                        }
+                    }
+                }
+                const uint32_t left = bs.n - cur;
+                b_loaded = left < 32u ? (int)left : 32;
+                b_cover = left > 32u ? w.get(r_p, 31) + (int)((w.get(r_w2, 31) >> HIT_RUN_SHIFT) & 7u) + 1 : n_loop;
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                lz_batches++; lz_hits += b_loaded;
+#endif
+            } else {
             if (i0 >= win_end) {
                 // ---- new window: lane l probes positions win_base + LZ_WIN_LANE*l + [0, LZ_WIN_LANE)
                 // (large enough that batches of 32 hits are normally full: ~2.4 % of the positions of
@@ -1039,32 +1246,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 for (int q = 0; q < LZ_WIN_WORDS; ++q) {
                     LZ_EACH(w, ln)
                     {
-                        const int pos0 = win_base + LZ_WIN_LANE * ln + 32 * q;
-                        uint32_t m = 0;
-                        if (pos0 < win_end) {
-                            const Rec a = ld_rec(pv.q + (pos0 >> 5)), b = ld_rec(pv.q + (pos0 >> 5) + 1);
-                            // positions whose mal-mer covers an N (rare: one test per 32 positions)
-                            uint32_t bad = 0;
-                            if (a.z | b.z) {
-                                const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
-                                uint64_t u = nz;
-                                for (int j = 1; j < P.mal; ++j) u |= nz >> j;
-                                bad = (uint32_t)u;
-                            }
-#if defined(__CUDA_ARCH__)
-#pragma unroll kScanUnroll
-#endif
-                            for (int t = 0; t < 32; ++t) {     // small body: the kernel is I-cache sensitive
-                                const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
-                                const uint32_t bi = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits);
-                                const uint32_t bw = ld_u32(pv.bitmap + (bi >> 5)) >> (bi & 31u);
-                                m = (m >> 1) | (bw << 31);      // bit of position t ends up at bit t
-                            }
-                            m &= ~bad;
-                            const int nv = win_end - pos0;
-                            if (nv < 32) m &= low_mask32(nv);
-                        }
-                        sc->hm[q][ln] = m;
+                        sc->hm[q][ln] = scan_word(pv, P, win_base + LZ_WIN_LANE * ln + 32 * q, win_end);
                     }
                 }
             }
@@ -1188,8 +1370,14 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 }
                 }
             }
+            }   // !BS::kStored
             chain_nx = 32;
         }
+        // what the speculative seed record says about the positions this batch covers (a stored record's
+        // scan may reach beyond the batch; an inline one never does)
+        int sK1 = spec_K1;
+        if (BS::kStored && sK1 > b_cover - i0) sK1 = b_cover - i0;
+        const int sks = spec_ks < sK1 ? spec_ks : 64;
 
         // ---- FAST PATH.  The walk stands right behind an anchor match taken from its record
         // (prediction on, no literals yet, seeds of the window known from the speculative scan) and
@@ -1199,7 +1387,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         //   * nothing at all for mqd+1 positions: the prediction expires.
         // Everything else (seeds, close matches, deferred or incomplete records) falls through to the
         // general code below, which re-derives the same step.
-        if (PT::kSpecSeeds && !RS::kActive && (s.pred < 0 || spec_K1 > 0)) {
+        if (PT::kSpecSeeds && !RS::kActive && (s.pred < 0 || sK1 > 0)) {
             Event ev;
             bool plain;
             int nx_next = -1;          // successor link of the event, when already fetched
@@ -1238,7 +1426,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
             plain = (ev.w2 & (HIT_DEFER | HIT_FWD)) == HIT_FWD;     // a complete record
             if (s.pred >= 0) {
                 if (ka > P.mqd) {
-                    if (spec_K1 > P.mqd && spec_ks >= 64) {
+                    if (sK1 > P.mqd && sks >= 64) {
                         // mqd+1 literal steps, then the prediction is dropped (:699-707) ...
                         s.i = i0 + P.mqd + 1;
                         s.lit = P.mqd + 1;
@@ -1251,7 +1439,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 } else {
                     int dist = ev.a_pos - (s.pred + ka);
                     if (dist < 0) dist = -dist;
-                    plain = plain && ka < spec_K1 && spec_ks > ka && ev.a_pos != 0 && dist > P.mrd;
+                    plain = plain && ka < sK1 && sks > ka && ev.a_pos != 0 && dist > P.mrd;
                 }
             }
             }
@@ -1345,8 +1533,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
         lz_pred_steps++;
 #endif
-        const bool use_spec = PT::kSpecSeeds && spec_K1 > 0;
-        if (use_spec && n > spec_K1) n = spec_K1;
+        const bool use_spec = PT::kSpecSeeds && sK1 > 0;
+        if (use_spec && n > sK1) n = sK1;
         // the first anchor record inside the chunk that counts here (position 0 == "none", :604)
         const Event eva = next_event(w, r_p, r_pos, r_w2, r_w3, i0, i0 + n, true);
         const int ja = eva.j;
@@ -1357,7 +1545,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         Planes64 Q{};                    // loaded only when a seed has to be looked at
         const int d_lo = -(ns - 1), d_hi = lit0 + P.mrd;
         uint64_t cand;
-        if (use_spec) cand = spec_ks < ns ? 1ull << spec_ks : 0ull;   // only the first seed matters
+        if (use_spec) cand = sks < ns ? 1ull << sks : 0ull;   // only the first seed matters
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
         if (use_spec) {   // TEST ONLY (tests/emul): the record must agree with the diagonal scan
             uint64_t chk = 0;
@@ -1489,12 +1677,27 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     return r;
 }
 
+// one-kernel form: the warp builds its batches itself
+template <class W, class PT, class RS>
+LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc, RS& rt)
+{
+    const InlineBatches ib{};
+    return parse_pair(w, pv, P, sc, rt, ib);
+}
 // the counting kernel: no region records
 template <class W, class PT>
 LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* sc)
 {
     NoRegions none;
     return parse_pair(w, pv, P, sc, none);
+}
+// the walk over stored records (staged pipeline)
+template <class W, class PT>
+LZ_HD PairResult walk_pair(W& w, const PairView& pv, const PT& P, const Rec* recs, uint32_t n_recs)
+{
+    NoRegions none;
+    const StoredBatches sb{recs, n_recs};
+    return parse_pair(w, pv, P, (WarpScratch*)nullptr, none, sb);
 }
 
 }  // namespace lzani

@@ -60,7 +60,35 @@ void build_index(HostIndex& ix, const HostSeq& s, const Prm& P)
     }
 }
 
+// the staged pipeline of kernels.cu for one pair: k_scan_hits / k_expand_hits / k_hit_records element by
+// element, then the walk over the stored records (k_walk_pairs)
+template <class PT>
+PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
+{
+    const int n_loop = pv.Dq - P.msl;
+    const int n_words = n_loop > 0 ? (n_loop + 31) / 32 : 0;
+    std::vector<HitEntry> list;
+    std::vector<uint32_t> coarse(coarse_words(pv.bbits));
+    for (uint32_t c = 0; c < coarse.size(); ++c) coarse[c] = coarse_fold_word(pv.bitmap, pv.bbits, c);
+    for (int wd = 0; wd < n_words; ++wd) {
+        const uint32_t m = scan_word_coarse(pv, P, 32 * wd, n_loop, coarse.data());
+        if (m != scan_word(pv, P, 32 * wd, n_loop)) ++lz_spec_mismatches;     // two-level scan == exact scan
+        uint32_t f = run_first_bits(m);
+        while (f) {
+            const int b = ctz32(f);
+            f &= f - 1u;
+            list.push_back(HitEntry{0u, (uint32_t)(32 * wd + b) | ((uint32_t)run_following(m, b) << HIT_ENTRY_RUN_SHIFT)});
+        }
+    }
+    std::vector<Rec> recs(list.size() + 1);
+    for (size_t t = 0; t < list.size(); ++t) recs[t] = hit_record(pv, P, n_loop, list.data(), t, list.size(), true, [] {});
+    return walk_pair(w, pv, P, recs.data(), (uint32_t)list.size());
+}
+
 }  // namespace
+
+static bool staged = false;
+extern "C" void lzani_emul_set_staged(int on) { staged = on != 0; }
 
 extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const uint8_t* const* data,
                                       const uint32_t* len, uint32_t n_rows, const uint32_t* ref_ids,
@@ -97,7 +125,10 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 pv.table = ix.table.data(); pv.tbits = ix.tbits;
                 // same dispatch as launch_parse(): compile-time defaults or run-time parameters
                 PairResult res;
-                if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch); }
+                if (staged) {
+                    if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = staged_pair(w, pv, D); }
+                    else res = staged_pair(w, pv, P);
+                } else if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch); }
                 else res = parse_pair(w, pv, P, &scratch);
                 out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
                 ++k;

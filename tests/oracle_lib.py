@@ -114,3 +114,8 @@ class Emul(_Checker):
     def __init__(self):
         subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "tests", "emul")], check=True)
         super().__init__(EMUL_SO, "lzani_emul")
+
+    def set_staged(self, on: bool):
+        """False: the one-kernel form (the warp builds its batches itself); True: the staged pipeline
+        (hit records computed ahead per query position, the walk loads them)."""
+        self.lib.lzani_emul_set_staged(1 if on else 0)

@@ -15,9 +15,14 @@ synth = importlib.import_module("lz-ani_b200.synth")
 GOLD = np.load(os.path.join(os.path.dirname(mg.__file__), "golden.npz"))
 
 
-@pytest.fixture(scope="module")
-def emul():
-    return Emul()
+@pytest.fixture(scope="module", params=["staged", "one_kernel"])
+def emul(request):
+    """Both forms of the parse: the staged pipeline (the product's default) and the one-kernel form
+    (regions kernel, LZANI_STAGED=0)."""
+    e = Emul()
+    e.set_staged(request.param == "staged")
+    yield e
+    e.set_staged(False)
 
 
 @pytest.mark.parametrize("case", list(mg.CASES))
