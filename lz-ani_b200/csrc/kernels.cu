@@ -292,6 +292,22 @@ k_hit_records(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, c
     if (live) reinterpret_cast<uint4*>(out)[t] = make_uint4(o.x, o.y, o.z, o.w);
 }
 
+// S3b.  Successor links: record t keeps the offset of its successor only if the walk's next step after t
+// is a plain fast-path event on that successor (verified_link).  Reads the records as k_hit_records left
+// them; only bits [29,32) of x change (the position bits other threads read stay as they are).
+template <class PT>
+__global__ void __launch_bounds__(256)
+k_link_records(Rec* __restrict__ hit_recs, const uint32_t* __restrict__ rec_total, PT P)
+{
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= *rec_total) return;
+    const Rec a = ld_rec(hit_recs + t);
+    const uint32_t d = a.x >> HIT_ENTRY_RUN_SHIFT;
+    if (!d) return;
+    const uint32_t keep = verified_link(P, a, ld_rec(hit_recs + t + d));
+    if (keep != d) hit_recs[t].x = a.x & (uint32_t)(LZ_STAGED_MAX_POS - 1);
+}
+
 template <class PT>
 __global__ void __launch_bounds__(LZ_WALK_THREADS, LZ_WALK_MIN_BLOCKS)
 k_walk_pairs(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off,
@@ -524,6 +540,13 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
         cudaError_t e = with_prm(P, [&](auto PT) {
             k_hit_records<<<(unsigned)((n_recs + LZ_RECORD_THREADS - 1) / LZ_RECORD_THREADS), LZ_RECORD_THREADS, 0, st>>>(
                 recs, B.desc, B.list, B.rec_off + n_words, PT, bitmap_pool, table_pool, B.recs);
+            return cudaGetLastError();
+        });
+        if (e != cudaSuccess) return e;
+    }
+    if (n_recs) {
+        cudaError_t e = with_prm(P, [&](auto PT) {
+            k_link_records<<<(unsigned)((n_recs + 255) / 256), 256, 0, st>>>(B.recs, B.rec_off + n_words, PT);
             return cudaGetLastError();
         });
         if (e != cudaSuccess) return e;

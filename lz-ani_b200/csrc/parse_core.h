@@ -774,6 +774,8 @@ LZ_HD void hit_extend(const PairView& pv, const PT& P, int p, int best_pos, uint
     }
 }
 
+constexpr uint32_t KV_KEEP = 1u << 16;
+constexpr int KV_LINK_SHIFT = 17;
 struct ParseState {
     int i, pred, lit;            // query position, ref_pred_pos (<0: none), cur_lit_run_len
     int rs, re, kept_end;        // prev_region_start / prev_region_end / end of last kept region
@@ -1108,7 +1110,7 @@ LZ_HD Rec hit_record(const PairView& pv, const PT& P, int n_loop, const HitEntry
     HitEntry e; e.pair = 0; e.pr = 0;
     if (live) e = list[t];
     const int p = (int)(e.pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
-    uint32_t pos = 0, w2 = 0, w3 = 0;
+    uint32_t pos = 0, w2 = 0, w3 = 0, succ = 0;
     if (live) hit_probe(pv, P, p, pos, w2);
     w2 |= (e.pr >> HIT_ENTRY_RUN_SHIFT) << HIT_RUN_SHIFT;
     sync();
@@ -1119,14 +1121,55 @@ LZ_HD Rec hit_record(const PairView& pv, const PT& P, int n_loop, const HitEntry
         // last position of the loop
         const int si0 = p + (int)(w2 & 63u) + (int)((w2 >> 6) & 63u);
         int lim_p = n_loop - 1;
+        bool inside = false;                 // the walk would come to stand inside a run on the way
         for (uint64_t u = t + 1; u < total && list[u].pair == e.pair; ++u) {
             const int pu = (int)(list[u].pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
-            if (pu >= si0) { lim_p = pu; break; }
+            if (pu >= si0) {
+                lim_p = pu;
+                if (!inside && u - t <= 7u) succ = (uint32_t)(u - t);
+                break;
+            }
+            if (pu + (int)(list[u].pr >> HIT_ENTRY_RUN_SHIFT) >= si0) inside = true;
         }
         hit_spec(pv, P, p, lim_p, pos, w2, w3);
+        if (!((w3 >> 18) & 63u)) succ = 0;   // no speculative seed record: the walk goes through the general code
     }
-    o.x = (uint32_t)p; o.y = pos; o.z = w2; o.w = w3;
+    o.x = (uint32_t)p | (succ << HIT_ENTRY_RUN_SHIFT); o.y = pos; o.z = w2; o.w = w3;
     return o;
+}
+
+// ---- successor links (k_link_records, one thread per record).  hit_record() left in x[29,32) the offset of
+// the first record at or after the window its record opens (0: none).  If the walk takes record `a` entirely
+// from its fields (the fast path of parse_pair), what happens next depends on nothing but a and that
+// successor b: this decides whether it is again one of the two plain fast-path events -- b inside the window,
+// no seed before or at it, far from the prediction; or nothing for mqd+1 positions (the prediction expires)
+// and b next -- with b's backward record usable whatever region was kept last (the literal run before b is at
+// least qi_b - si0_a long).  The offset is kept only then; the walk follows such links without re-deriving
+// anything (parse_pair, "chain").
+template <class PT>
+LZ_HD uint32_t verified_link(const PT& P, const Rec& a, const Rec& b)
+{
+    const uint32_t d = a.x >> HIT_ENTRY_RUN_SHIFT;
+    if (!d) return 0;
+    if ((a.z & (HIT_DEFER | HIT_FWD | HIT_BWD)) != (HIT_FWD | HIT_BWD)) return 0;
+    if ((b.z & (HIT_LIVE | HIT_DEFER | HIT_FWD | HIT_BWD)) != (HIT_LIVE | HIT_FWD | HIT_BWD)) return 0;
+    const int adv = (int)(a.z & 63u) + (int)((a.z >> 6) & 63u);
+    const int si0 = (int)(a.x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) + adv, sP0 = (int)a.y + adv;
+    const int K1 = (int)((a.w >> 18) & 63u), ks = (int)((a.w >> 24) & 127u);
+    const int qb = (int)(b.x & (uint32_t)(LZ_STAGED_MAX_POS - 1)), pb = (int)b.y;
+    const int ka = qb - si0;
+    if (ka <= 0 || K1 <= 0) return 0;
+    if (ka > P.mqd) {
+        if (!(K1 > P.mqd && ks >= 64)) return 0;
+    } else {
+        int dist = pb - (sP0 + ka);
+        if (dist < 0) dist = -dist;
+        if (!(ka < K1 && ks > ka && pb != 0 && dist > P.mrd)) return 0;
+    }
+    int lim = ka < qb ? ka : qb;
+    if (pb < lim) lim = pb;
+    if (lim < (int)((b.w >> 12) & 63u)) return 0;
+    return d;
 }
 
 // where parse_pair() gets its batches of hit records from
@@ -1174,12 +1217,13 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     int b_cover = 0;                   // every hit in [batch start, b_cover) has a record
     typename W::template Lanes<uint32_t> r_pos, r_w2, r_w3;
     typename W::template Lanes<int> r_p, r_nx;     // r_nx: successor links (see "successor links" below)
+    typename W::template Lanes<uint32_t> r_kv;     // stored batches: chain summary of each record
     uint32_t cur = 0;                  // stored batches: first record of the current batch
     int b_loaded = 0;                  //                 and how many records it holds
     LZ_EACH(w, ln)
     {
         if (!BS::kStored) for (int q = 0; q < LZ_WIN_WORDS; ++q) sc->hm[q][ln] = 0;
-        r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; r_nx[ln] = 32;
+        r_pos[ln] = 0; r_w2[ln] = 0; r_w3[ln] = 0; r_p[ln] = 0x7FFFFFFF; r_nx[ln] = 32; r_kv[ln] = 0;
     }
 
     for (;;) {
@@ -1202,8 +1246,17 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         const uint32_t idx = cur + (uint32_t)ln;
                         Rec h; h.x = 0x7FFFFFFFu; h.y = 0; h.z = 0; h.w = 0;
                         if (idx < bs.n) h = ld_rec(bs.recs + idx);
-                        r_p[ln] = (int)h.x; r_pos[ln] = h.y; r_w2[ln] = h.z; r_w3[ln] = h.w;
-                        behind[ln] = idx < bs.n && (int)h.x + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
+                        const int hp = (int)(h.x & 0x7FFFFFFFu & ~(7u << HIT_ENTRY_RUN_SHIFT) ) | (idx < bs.n ? 0 : 0x7FFFFFFF);
+                        r_p[ln] = hp; r_pos[ln] = h.y; r_w2[ln] = h.z; r_w3[ln] = h.w;
+                        // chain summary: matches / literals of the region the record opens when taken from its
+                        // fields, whether that region is kept, link offset
+                        {
+                            const int len = (int)(h.z & 63u), fwd = (int)((h.z >> 6) & 63u), fm = (int)((h.z >> 12) & 63u);
+                            const int back = (int)(h.w & 63u), bm = (int)((h.w >> 6) & 63u);
+                            r_kv[ln] = (uint32_t)(bm + len + fm) | ((uint32_t)(back - bm + fwd - fm) << 8) |
+                                       (back + len + fwd >= P.reg ? KV_KEEP : 0u) | ((h.x >> HIT_ENTRY_RUN_SHIFT) << KV_LINK_SHIFT);
+                        }
+                        behind[ln] = idx < bs.n && hp + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
                     }
                     const int nb = popc32(w.ballot(behind));
                     if (!nb) break;
@@ -1218,7 +1271,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                                 far[ln] = 0;
                                 if (idx < bs.n) {
                                     const Rec h = ld_rec(bs.recs + idx);
-                                    far[ln] = (int)h.x + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
+                                    far[ln] = (int)(h.x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) + (int)((h.z >> HIT_RUN_SHIFT) & 7u) < i0;
                                 }
                             }
                             const int nf = popc32(w.ballot(far));
@@ -1485,6 +1538,85 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
                     lz_matches++; lz_fast++;
 #endif
+                    if (BS::kStored) {
+                        // ---- chain: verified successor links (verified_link) inside the batch.  Every step is a
+                        // distant match taken from its record right after one taken from its record: the region of
+                        // the record left behind is judged by its length, nothing else carries over.
+                        int j = ev.j;
+                        uint32_t v = w.get(r_kv, j);
+                        int d = (int)(v >> KV_LINK_SHIFT);
+                        if (d && run > 0 && j + d < b_loaded) {      // (run > 0: the entry record's region is the one its summary describes)
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                            ParseState chk = s;      // TEST ONLY (tests/emul): the serial fast path, step by step
+                            int chk_j = j;
+#endif
+                            do {
+                                if (v & KV_KEEP) {
+                                    s.totM += (int)(v & 255u);
+                                    s.totX += (int)((v >> 8) & 255u);
+                                    ++s.totN;
+                                    const uint32_t jw2 = w.get(r_w2, j);
+                                    s.kept_end = w.get(r_p, j) + (int)(jw2 & 63u) + (int)((jw2 >> 6) & 63u);
+                                }
+                                j += d;
+                                v = w.get(r_kv, j);
+                                d = (int)(v >> KV_LINK_SHIFT);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                                lz_matches++; lz_fast++; lz_chain++;
+#endif
+                            } while (d && j + d < b_loaded);
+                            const int cq = w.get(r_p, j), cp = (int)w.get(r_pos, j);
+                            const uint32_t cw2 = w.get(r_w2, j), cw3 = w.get(r_w3, j);
+                            const int back = (int)(cw3 & 63u), len = (int)(cw2 & 63u), fwd = (int)((cw2 >> 6) & 63u);
+                            s.curM = (int)(v & 255u);
+                            s.curX = (int)((v >> 8) & 255u);
+                            s.rs = cq - back;
+                            s.i = cq + len + fwd;
+                            s.pred = cp + len + fwd;
+                            s.re = s.i;
+                            spec_K1 = (int)((cw3 >> 18) & 63u);
+                            spec_ks = (int)((cw3 >> 24) & 127u);
+                            spec_x = (cw3 >> 31) ? -1 : (int)(cw2 >> HIT_X_SHIFT);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                            {   // TEST ONLY: replay the same steps with the serial rules of the fast path
+                                while (chk_j != j) {
+                                    const int dd = (int)(w.get(r_kv, chk_j) >> KV_LINK_SHIFT);
+                                    const int t = chk_j + dd;
+                                    const int tq = w.get(r_p, t), tp = (int)w.get(r_pos, t);
+                                    const uint32_t tw2 = w.get(r_w2, t), tw3 = w.get(r_w3, t);
+                                    const uint32_t aw2 = w.get(r_w2, chk_j), aw3 = w.get(r_w3, chk_j);
+                                    const int K1 = (int)((aw3 >> 18) & 63u), ks = (int)((aw3 >> 24) & 127u);
+                                    const int ka = tq - chk.i;
+                                    bool ok = (tw2 & (HIT_LIVE | HIT_DEFER | HIT_FWD)) == (HIT_LIVE | HIT_FWD) && K1 > 0 && (aw2 & HIT_FWD);
+                                    const Event e2 = next_event(w, r_p, r_pos, r_w2, r_w3, chk.i, 0x7FFFFFFF, false);
+                                    if (e2.j != t || e2.qi != tq) ok = false;
+                                    if (ka > P.mqd) ok = ok && K1 > P.mqd && ks >= 64;
+                                    else {
+                                        int dist = tp - (chk.pred + ka);
+                                        if (dist < 0) dist = -dist;
+                                        ok = ok && ka < K1 && ks > ka && tp != 0 && dist > P.mrd;
+                                    }
+                                    const bool keep = chk.rs >= 0 && chk.re - chk.rs >= P.reg;
+                                    const int kept_end = keep ? chk.re : chk.kept_end;
+                                    const int run = tq - kept_end;
+                                    int lim = run < tq ? run : tq;
+                                    if (tp < lim) lim = tp;
+                                    ok = ok && run > 0 && (tw2 & HIT_BWD) && lim >= (int)((tw3 >> 12) & 63u);
+                                    if (!ok) lz_spec_mismatches++;
+                                    if (keep) { chk.totM += chk.curM; chk.totX += chk.curX; ++chk.totN; chk.kept_end = kept_end; }
+                                    const int tb = (int)(tw3 & 63u), tbm = (int)((tw3 >> 6) & 63u);
+                                    const int tl = (int)(tw2 & 63u), tf = (int)((tw2 >> 6) & 63u), tfm = (int)((tw2 >> 12) & 63u);
+                                    chk.curM = tbm + tl + tfm; chk.curX = tb - tbm + tf - tfm;
+                                    chk.rs = tq - tb; chk.i = tq + tl + tf; chk.pred = tp + tl + tf; chk.lit = 0; chk.re = chk.i;
+                                    chk_j = t;
+                                }
+                                if (chk.i != s.i || chk.pred != s.pred || chk.rs != s.rs || chk.re != s.re || chk.kept_end != s.kept_end ||
+                                    chk.curM != s.curM || chk.curX != s.curX || chk.totM != s.totM || chk.totX != s.totX || chk.totN != s.totN)
+                                    lz_spec_mismatches++;
+                            }
+#endif
+                        }
+                    }
                     continue;
                 }
                 chain_nx = 32;             // backward record not usable: the general code takes this step

@@ -82,6 +82,14 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
     }
     std::vector<Rec> recs(list.size() + 1);
     for (size_t t = 0; t < list.size(); ++t) recs[t] = hit_record(pv, P, n_loop, list.data(), t, list.size(), true, [] {});
+    // k_link_records: the link of every record is decided from the records as hit_record() left them
+    std::vector<uint32_t> link(list.size());
+    for (size_t t = 0; t < list.size(); ++t) {
+        const uint32_t d = recs[t].x >> HIT_ENTRY_RUN_SHIFT;
+        link[t] = d ? verified_link(P, recs[t], recs[t + d]) : 0u;
+    }
+    for (size_t t = 0; t < list.size(); ++t)
+        recs[t].x = (recs[t].x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) | (link[t] << HIT_ENTRY_RUN_SHIFT);
     return walk_pair(w, pv, P, recs.data(), (uint32_t)list.size());
 }
 
