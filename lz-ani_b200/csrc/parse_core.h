@@ -577,6 +577,23 @@ LZ_HD ExtWord extend_in_word(uint32_t mw, int nv, bool more, const PT& P)
     return o;
 }
 
+// try_extend_forward / try_extend_backward when the walk ends inside the first stream word (nearly always:
+// with the default parameters a random continuation overflows the window after ~10 positions): one
+// broadcast comparison evaluated by every lane alike instead of the 1024-position cooperative chunk of
+// approx_extend().  false: the walk runs on into the next word -- use approx_extend().
+template <class PT>
+LZ_COLD bool approx_extend_short(const AnyStream& st, int limit, const PT& P, int& out_len, int& out_matches)
+{
+    out_len = 0;
+    out_matches = 0;
+    if (limit <= 0) return true;
+    const ExtWord e = extend_in_word(st.word(0), limit > 32 ? 32 : limit, limit > 32, P);
+    if (!e.complete) return false;
+    out_len = e.len;
+    out_matches = e.matches;
+    return true;
+}
+
 // ------------------------------------------------------------------------------------------
 // Speculative seed scan, evaluated by ONE lane for ITS hit ahead of the walk (msl == 7 kernels).
 // Should the walk take the hit's anchor as a match (with the forward extension of its record),
@@ -822,7 +839,7 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, RS& 
                 bm = (int)((w3 >> 6) & 63u);
             } else {
                 AnyStream bs{&pv, qi, best_pos, true};
-                approx_extend(w, bs, lim, P, back, bm);
+                if (!approx_extend_short(bs, lim, P, back, bm)) approx_extend(w, bs, lim, P, back, bm);
             }
         }
         s.curM = bm + best_len;
@@ -847,7 +864,7 @@ LZ_HD void take_match(W& w, const PairView& pv, const PT& P, ParseState& s, RS& 
         int lim = pv.Dq - qn;
         if (pv.Dr - pn < lim) lim = pv.Dr - pn;
         AnyStream fs{&pv, qn, pn, false};
-        approx_extend(w, fs, lim, P, fwd, fm);      // :691-695
+        if (!approx_extend_short(fs, lim, P, fwd, fm)) approx_extend(w, fs, lim, P, fwd, fm);      // :691-695
     }
     s.curM += fm;
     s.curX += fwd - fm;
@@ -1040,6 +1057,24 @@ LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int e
         }
         const uint32_t cbits = pv.bbits < (uint32_t)LZ_COARSE_BITS ? pv.bbits : (uint32_t)LZ_COARSE_BITS;
         const uint32_t cmask = (1u << cbits) - 1u;
+        if (2 * P.mal <= LZ_DIRECT_BITMAP_MAX_BITS) {
+            // direct-addressed bitmap: index = key = low-plane bits | high-plane bits << mal.  With the high
+            // plane shifted up by mal once per word the index is one funnel shift per plane and one select
+            // (the bits above 2*mal are dropped by the fold mask); the byte offset into the folded copy is
+            // taken straight from it.
+            const uint32_t km = low_mask32(P.mal);
+            const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
+            const uint32_t omask = (cmask >> 5) << 2;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
+#endif
+            for (int t = 0; t < 32; ++t) {
+                const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
+                const uint32_t sel = (lo & km) | (hs & ~km);
+                const uint32_t cwd = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(coarse) + ((sel >> 3) & omask));
+                m = funnel_r(m, funnel_r(cwd, 0u, (int)(sel & 31u)), 1);
+            }
+        } else {
 #if defined(__CUDA_ARCH__)
 #pragma unroll 8
 #endif
@@ -1048,6 +1083,7 @@ LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int e
             const uint32_t ci = bitmap_index(kmer_key(lo, hi, P.mal), P.mal, pv.bbits) & cmask;
             const uint32_t bw = coarse[ci >> 5] >> (ci & 31u);
             m = (m >> 1) | (bw << 31);
+        }
         }
         m &= ~bad;
         const int nv = end - pos0;

@@ -18,7 +18,8 @@ MARKS = [("equal_len_coop", "int equal_len_coop("), ("approx_extend", "void appr
          ("diag_helpers", "struct DiagWord"), ("extend_in_word", "struct ExtWord"), ("spec_first_seed", "struct V3"),
          ("hit_probe", "void hit_probe("), ("hit_extend", "void hit_extend("), ("take_match", "void take_match("), ("diag_seed_starts", "uint64_t diag_seed_starts("),
          ("best_seed", "void best_seed("), ("pp:init", "PairResult parse_pair("), ("pp:window_scan", "// ---- new window"),
-         ("pp:batch_list", "// ---- new batch"), ("pp:batch_eval", "b_cover = total <= 32"), ("pp:batch_spec", "if (PT::kSpecSeeds && !RS::kActive && P.mqd <= SPEC_MAX_K)"), ("pp:fast", "// ---- FAST PATH"), ("next_event", "struct Event {"), ("pp:nopred", "// ---- no prediction"),
+         ("pp:batch_list", "// ---- new batch"), ("pp:batch_eval", "b_cover = total <= 32"), ("pp:batch_spec", "if (PT::kSpecSeeds && !RS::kActive && P.mqd <= SPEC_MAX_K)"), ("pp:fast", "// ---- FAST PATH"), ("pp:stored_load", "// ---- next batch: the first <= 32 stored"), ("pp:inline_batch", "} else {\n            if (i0 >= win_end)"), ("pp:chain", "// ---- chain: verified successor links"), ("pp:sK1", "// what the speculative seed record says"),
+         ("scan_word", "LZ_HD uint32_t scan_word("), ("scan_coarse", "LZ_HD uint32_t scan_word_coarse("), ("hit_spec", "void hit_spec("), ("hit_record", "LZ_HD Rec hit_record("), ("verified_link", "LZ_HD uint32_t verified_link("), ("next_event", "struct Event {"), ("pp:nopred", "// ---- no prediction"),
          ("pp:pred", "// ---- prediction mode"), ("pp:take", "if (matched) {"), ("pp:tail", "// tail (:710-713)")]
 
 
