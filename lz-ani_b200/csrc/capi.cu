@@ -72,9 +72,11 @@ struct lzani_ctx {
         cudaStream_t st = nullptr;
         cudaEvent_t done = nullptr;
         uint32_t* h_total = nullptr;      // pinned: records of the chunk
+        uint32_t* mc = nullptr;           // all2all scan: k-mer x reference bit matrix (4^mal words)
     } slot[2];
+    int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
-    uint64_t staged_words = 48ull << 20;  // words per chunk (LZANI_STAGED_WORDS)
+    uint64_t staged_words = 96ull << 20;  // words per chunk (LZANI_STAGED_WORDS)
     int walk_blocks_per_sm = 1;
     double rec_per_word = 1.0;            // observed hit runs per 32 query positions (chunk sizing)
     uint32_t staged_chunks = 0;           // of the last run
@@ -216,6 +218,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
     c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
     if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
+    if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
     if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) c->staged_words = (uint64_t)v; }
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
@@ -240,6 +243,7 @@ extern "C" void lzani_destroy(lzani_ctx* c)
         cudaFree(c->d_eff_len); cudaFree(c->d_pairs);
         for (auto& sl : c->slot) {
             free_slot(sl);
+            cudaFree(sl.mc);
             cudaFree(sl.B.counter);
             if (sl.h_total) cudaFreeHost(sl.h_total);
             if (sl.done) cudaEventDestroy(sl.done);
@@ -595,11 +599,14 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         if (by_recs < w_target) w_target = by_recs;
                         const uint64_t p_max = (uint64_t)1 << 19;
                         uint64_t k = k_next, wsum = 0;
+                        while (row_off[j_cur + 1] <= k) ++j_cur;
+                        const uint32_t j_first = j_cur;
                         while (k < ke && k - k_next < p_max) {
                             while (row_off[j_cur + 1] <= k) ++j_cur;
                             if (!q_ids && k == row_off[j_cur]) {          // a whole dense row at once
                                 const uint64_t rw = words_all - wq[row_ref[j_cur]], np = row_off[j_cur + 1] - k;
                                 if (wsum + rw <= w_target && k - k_next + np <= p_max) { wsum += rw; k += np; continue; }
+                                if (k > k_next && k_next == row_off[j_first]) break;   // keep the chunk made of whole rows
                             }
                             const uint32_t w1 = wq[pair_q(j_cur, k)];
                             if (k > k_next && wsum + w1 > w_target) break;
@@ -616,9 +623,21 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                                                  std::max(ch.words, std::max(sl.words_cap, c->slot[0].words_cap)),
                                                  std::max(sl.recs_cap, c->slot[0].recs_cap))) return rc;
                     }
+                    // all2all form of the scan when the chunk is made of whole dense rows and the bitmaps are direct
+                    MatrixScan mx{};
+                    bool use_mx = false;
+                    if (!q_ids && c->matrix_scan && 2 * P.mal <= 22 && n <= 65535u && np) {
+                        const uint32_t ja = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k0) - row_off.begin()) - 1;
+                        const uint32_t jb = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k1 - 1) - row_off.begin());
+                        if (row_off[ja] == ch.k0 && row_off[jb] == ch.k1) {
+                            if (!sl.mc) LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) << (2 * P.mal)));
+                            mx.mc = sl.mc; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
+                            use_mx = true;
+                        }
+                    }
                     LZ_CUDA(c, launch_staged_scan(sl.st, sl.B, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
                                                   c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, ch.k0, (uint32_t)np,
-                                                  ch.words, P, c->d_bitmap, c->n_sm));
+                                                  ch.words, P, c->d_bitmap, c->n_sm, use_mx ? &mx : nullptr));
                     LZ_CUDA(c, cudaMemcpyAsync(sl.h_total, sl.B.rec_off + ch.words, sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.st));
                     LZ_CUDA(c, cudaStreamSynchronize(sl.st));
                     const uint64_t n_hit = *sl.h_total;
@@ -640,7 +659,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     }
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
                                                   c->d_bitmap, c->d_table, c->d_out));
-                    T.launches += 4;
+                    T.launches += 5;
                     ++c->staged_chunks;
                 }
                 for (auto& sl : c->slot) {

@@ -137,8 +137,9 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 //   S1 k_scan_hits     thread per word        hit mask of 32 query positions (anchor presence bitmap)
 //      (exclusive scan of the run counts -> rec_off)
 //   S2 k_expand_hits   thread per word        hit list: (pair, position, run length) per hit run
-//   S3 k_hit_records   thread per hit run     table probe, match length, both approximate extensions,
-//                                             speculative seed scan -> one 16-byte record
+//   S3 k_hit_probe     thread per hit run     table probe, match length, both approximate extensions
+//      k_hit_spec      thread per hit run     speculative seed scan (jobs sorted by length per block)
+//      k_link_records  thread per hit run     successor links -> one 16-byte record per hit run
 //   S4 k_walk_pairs    warp per pair          the state machine of parser.cpp:501-708 over the records
 template <class PT>
 __global__ void __launch_bounds__(256)
@@ -241,6 +242,76 @@ k_scan_hits(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, con
     }
 }
 
+// S1m.  The all2all form of S1 (dense rows, direct-addressed bitmaps): instead of one probe per query
+// position and REFERENCE, the presence bitmaps of up to 32 references of the chunk are transposed into one
+// 32-bit word per k-mer (k_bitmap_matrix: Mc[key] bit i <=> reference i has the k-mer), a query word is
+// scanned once against all of them -- one 4-byte gather per position -- and a register transpose turns the
+// 32 gathered words into the 32 hit masks.  ~40x fewer instructions per (pair, word) than the probe scan.
+__global__ void __launch_bounds__(256)
+k_bitmap_matrix(const uint32_t* __restrict__ bitmap_pool, const RefIndex* __restrict__ row_idx, uint32_t nr,
+                uint32_t n_key_words, uint32_t* __restrict__ mc)
+{
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= n_key_words) return;
+    uint32_t a[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) a[i] = (uint32_t)i < nr ? bitmap_pool[row_idx[i].bitmap_word + t] : 0u;
+    transpose32(a);
+    uint4* o = reinterpret_cast<uint4*>(mc + 32ull * t);
+#pragma unroll
+    for (int b = 0; b < 8; ++b) o[b] = make_uint4(a[4 * b], a[4 * b + 1], a[4 * b + 2], a[4 * b + 3]);
+}
+
+// grid: (blocks over the words of a query, query id).  row_ref / row_off point at the first of the nr rows
+// of the block; chunk_k0 = first pair of the chunk (global pair number, as in row_off).
+template <class PT>
+__global__ void __launch_bounds__(128)
+k_scan_matrix(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta, const uint32_t* __restrict__ row_ref,
+              const uint64_t* __restrict__ row_off, uint32_t nr, uint64_t chunk_k0,
+              const uint32_t* __restrict__ word_off, PT P, const uint32_t* __restrict__ mc, uint32_t key_mask,
+              uint32_t* __restrict__ hm, uint32_t* __restrict__ wpair)
+{
+    __shared__ uint32_t s_ref[32];
+    __shared__ uint32_t s_pl0[32];
+    const uint32_t q = blockIdx.y;
+    if (threadIdx.x < 32) {
+        const uint32_t i = threadIdx.x;
+        uint32_t r = 0xFFFFFFFFu, p0 = 0;
+        if (i < nr) {
+            r = row_ref[i];
+            p0 = (uint32_t)(row_off[i] - chunk_k0) + (q < r ? q : q - 1u);     // dense row: the (q - [q > r])-th pair
+        }
+        s_ref[i] = r;
+        s_pl0[i] = p0;
+    }
+    __syncthreads();
+    const SeqMeta mq = meta[q];
+    const int n_loop = (int)mq.len + P.mrd - P.msl;
+    const uint32_t w = blockIdx.x * 128u + threadIdx.x;
+    if (n_loop <= 0 || w >= (uint32_t)((n_loop + 31) / 32)) return;
+    const Rec* qr = recs + mq.q_rec;
+    const Rec a = ld_rec(qr + w), b = ld_rec(qr + w + 1);
+    const uint32_t km = low_mask32(P.mal);
+    const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
+    uint32_t v[32];
+#pragma unroll
+    for (int t = 0; t < 32; ++t) {
+        const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
+        v[t] = __ldg(mc + (((lo & km) | (hs & ~km)) & key_mask));
+    }
+    transpose32(v);
+    const uint32_t valid = scan_valid_mask(a, b, P.mal, (int)(32u * w), n_loop);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        if ((uint32_t)i < nr && s_ref[i] != q) {
+            const uint32_t pl = s_pl0[i];
+            const uint32_t gw = word_off[pl] + w;
+            hm[gw] = v[i] & valid;
+            wpair[gw] = pl;
+        }
+    }
+}
+
 // input of the second scan: hit runs per word
 struct RunCount {
     __host__ __device__ __forceinline__ uint32_t operator()(uint32_t m) const { return (uint32_t)__builtin_popcount(run_first_bits(m)); }
@@ -272,27 +343,84 @@ struct WarpSyncFn {
     __device__ __forceinline__ void operator()() const { __syncwarp(); }
 };
 
+// S3a.  One thread per hit run: table probe, match length, both approximate extensions (latency-bound:
+// random table and sequence loads; few registers, full occupancy).
 template <class PT>
 __global__ void __launch_bounds__(LZ_RECORD_THREADS)
-k_hit_records(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
-              const uint32_t* __restrict__ rec_total, PT P, const uint32_t* __restrict__ bitmap_pool,
-              const uint64_t* __restrict__ table_pool, Rec* __restrict__ out)
+k_hit_probe(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
+            const uint32_t* __restrict__ rec_total, PT P, const uint32_t* __restrict__ bitmap_pool,
+            const uint64_t* __restrict__ table_pool, Rec* __restrict__ out)
 {
     const uint32_t total = *rec_total;
     const uint32_t t = blockIdx.x * (uint32_t)LZ_RECORD_THREADS + threadIdx.x;
     const bool live = t < total;
     PairView pv{};
-    int n_loop = 0;
-    if (live) {
-        const PairDesc d = desc[list[t].pair];
-        pv = view_of(d, recs, bitmap_pool, table_pool);
-        n_loop = d.Dq - P.msl;
-    }
-    const Rec o = hit_record(pv, P, n_loop, list, (uint64_t)t, (uint64_t)total, live, WarpSyncFn{});
+    if (live) pv = view_of(desc[list[t].pair], recs, bitmap_pool, table_pool);
+    const Rec o = hit_record_probe(pv, P, list, (uint64_t)t, live, WarpSyncFn{});
     if (live) reinterpret_cast<uint4*>(out)[t] = make_uint4(o.x, o.y, o.z, o.w);
 }
 
-// S3b.  Successor links: record t keeps the offset of its successor only if the walk's next step after t
+// S3b.  The speculative seed scans (instruction-bound: ~40 instructions per row, up to mqd+7 rows).  The
+// scan length K differs from record to record (it ends at the next hit run), so the jobs of a thread block
+// are counting-sorted by K through shared memory and dealt out longest first: the lanes of a warp then
+// run about the same number of rows.
+template <class PT>
+__global__ void __launch_bounds__(LZ_SPEC_THREADS)
+k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
+           const uint32_t* __restrict__ rec_total, PT P, Rec* hit_recs)
+{
+    struct Item { const Rec* q; const Rec* r; int si0, sP0, K; uint32_t succ; };
+    __shared__ uint32_t s_hist[64];
+    __shared__ uint16_t s_order[LZ_SPEC_THREADS];
+    __shared__ Item s_item[LZ_SPEC_THREADS];
+    const uint32_t total = *rec_total;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * (uint32_t)LZ_SPEC_THREADS + tid;
+    if (tid < 64) s_hist[tid] = 0;
+    __syncthreads();
+    SpecJob j; j.si0 = 0; j.sP0 = 0; j.K = -1; j.succ = 0; j.need = false;
+    if (t < total) {
+        const Rec rec = ld_rec(hit_recs + t);
+        const PairDesc d = desc[list[t].pair];
+        j = hit_spec_job(P, d.Dq - P.msl, list, (uint64_t)t, (uint64_t)total, rec);
+        if (j.need) s_item[tid] = Item{recs + d.q_rec, recs + d.r_rec, j.si0, j.sP0, j.K, j.succ};
+    }
+    uint32_t key = 63, rank = 0;
+    if (j.need) {
+        key = j.K < 0 ? 62u : (uint32_t)(SPEC_MAX_K - j.K);        // K <= SPEC_MAX_K = 57
+        rank = atomicAdd(&s_hist[key], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {                                                 // exclusive prefix over the 64 bins
+        const uint32_t a = s_hist[2 * tid], b = s_hist[2 * tid + 1];
+        uint32_t v = a + b;
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xFFFFFFFFu, v, dlt);
+            if ((int)tid >= dlt) v += u;
+        }
+        s_hist[2 * tid] = v - a - b;
+        s_hist[2 * tid + 1] = v - b;
+    }
+    __syncthreads();
+    if (j.need) s_order[s_hist[key] + rank] = (uint16_t)tid;
+    const uint32_t n_jobs = s_hist[63];                             // bin 63 is never used: its prefix is the job count
+    __syncthreads();
+    if (tid < n_jobs) {
+        const uint32_t o = s_order[tid];
+        const Item it = s_item[o];
+        PairView pv{};
+        pv.q = it.q; pv.r = it.r;
+        const int ks = spec_first_seed(pv, P, it.si0, it.sP0, it.K);
+        const uint32_t to = blockIdx.x * (uint32_t)LZ_SPEC_THREADS + o;
+        Rec r2 = ld_rec(hit_recs + to);
+        SpecJob jj; jj.si0 = it.si0; jj.sP0 = it.sP0; jj.K = it.K; jj.succ = it.succ; jj.need = true;
+        hit_spec_finish(r2, jj, ks);
+        reinterpret_cast<uint4*>(hit_recs)[to] = make_uint4(r2.x, r2.y, r2.z, r2.w);
+    }
+}
+
+// S3c.  Successor links: record t keeps the offset of its successor only if the walk's next step after t
 // is a plain fast-path event on that successor (verified_link).  Reads the records as k_hit_records left
 // them; only bits [29,32) of x change (the position bits other threads read stay as they are).
 template <class PT>
@@ -496,7 +624,8 @@ size_t staged_scan_bytes(uint64_t n_items)
 cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
                                const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,
                                uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint32_t n_pairs,
-                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks)
+                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks,
+                               const MatrixScan* mx)
 {
     cudaError_t e = with_prm(P, [&](auto PT) {
         k_pair_desc<<<n_pairs / 256 + 1, 256, 0, st>>>(meta, row_ref, row_idx, row_off, n_rows, q_ids, pair_begin, n_pairs,
@@ -507,7 +636,24 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
     size_t tb = B.tmp_bytes;
     e = cub::DeviceScan::ExclusiveSum(B.tmp, tb, (const uint32_t*)B.n_words, B.word_off, (int64_t)n_pairs + 1, st);
     if (e != cudaSuccess) return e;
-    if (n_words) {
+    if (n_words && mx) {
+        // all2all form: blocks of <= 32 whole rows
+        const uint32_t key_words = ((1u << (2 * P.mal)) + 31u) / 32u;
+        const uint32_t key_mask = (1u << (2 * P.mal)) - 1u;
+        for (uint32_t i0 = 0; i0 < mx->n_rows_chunk; i0 += 32) {
+            const uint32_t nr = mx->n_rows_chunk - i0 < 32u ? mx->n_rows_chunk - i0 : 32u;
+            k_bitmap_matrix<<<(key_words + 255) / 256, 256, 0, st>>>(bitmap_pool, row_idx + mx->row_first + i0, nr, key_words, mx->mc);
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+            e = with_prm(P, [&](auto PT) {
+                const dim3 grid((mx->max_words + 127) / 128, mx->n_seqs);
+                k_scan_matrix<<<grid, 128, 0, st>>>(recs, meta, row_ref + mx->row_first + i0, row_off + mx->row_first + i0, nr,
+                                                    pair_begin, B.word_off, PT, mx->mc, key_mask, B.hm, B.wpair);
+                return cudaGetLastError();
+            });
+            if (e != cudaSuccess) return e;
+        }
+    } else if (n_words) {
         e = with_prm(P, [&](auto PT) {
             using K = decltype(PT);
             static bool attr_set = false;      // per instantiation
@@ -538,8 +684,13 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
     }
     if (n_recs) {
         cudaError_t e = with_prm(P, [&](auto PT) {
-            k_hit_records<<<(unsigned)((n_recs + LZ_RECORD_THREADS - 1) / LZ_RECORD_THREADS), LZ_RECORD_THREADS, 0, st>>>(
+            k_hit_probe<<<(unsigned)((n_recs + LZ_RECORD_THREADS - 1) / LZ_RECORD_THREADS), LZ_RECORD_THREADS, 0, st>>>(
                 recs, B.desc, B.list, B.rec_off + n_words, PT, bitmap_pool, table_pool, B.recs);
+            cudaError_t e1 = cudaGetLastError();
+            if (e1 != cudaSuccess) return e1;
+            if (decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K)
+                k_hit_spec<<<(unsigned)((n_recs + LZ_SPEC_THREADS - 1) / LZ_SPEC_THREADS), LZ_SPEC_THREADS, 0, st>>>(
+                    recs, B.desc, B.list, B.rec_off + n_words, PT, B.recs);
             return cudaGetLastError();
         });
         if (e != cudaSuccess) return e;

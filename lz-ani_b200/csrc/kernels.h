@@ -21,7 +21,10 @@
 #define LZ_WALK_MIN_BLOCKS 5
 #endif
 #ifndef LZ_RECORD_THREADS
-#define LZ_RECORD_THREADS 128
+#define LZ_RECORD_THREADS 256
+#endif
+#ifndef LZ_SPEC_THREADS
+#define LZ_SPEC_THREADS 256
 #endif
 
 namespace lzani {
@@ -70,13 +73,22 @@ struct StagedBufs {
     void* tmp; size_t tmp_bytes;  // CUB scan scratch
     unsigned long long* counter;
 };
+// all2all form of the scan (k_bitmap_matrix + k_scan_matrix): the chunk is made of whole dense rows
+struct MatrixScan {
+    uint32_t* mc;                 // [4^mal] one word per k-mer: which of the block's <= 32 references have it
+    uint32_t row_first;           // first row of the chunk, relative to the row arrays handed to the launch
+    uint32_t n_rows_chunk;
+    uint32_t n_seqs;              // queries = every sequence
+    uint32_t max_words;           // longest query, in 32-position words
+};
 int walk_blocks_per_sm(const Prm& P);
 size_t staged_scan_bytes(uint64_t n_items);
 // S0, scan, S1, scan: afterwards rec_off[n_words] holds the number of records of the chunk
 cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
                                const uint32_t* row_ref, const RefIndex* row_idx, const uint64_t* row_off,
                                uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint32_t n_pairs,
-                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks);
+                               uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks,
+                               const MatrixScan* mx = nullptr);
 // S2, S3, S4
 cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
                                uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,

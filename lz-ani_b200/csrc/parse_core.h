@@ -1101,6 +1101,45 @@ LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int e
     }
     return m;
 }
+// ---- 32 x 32 bit-matrix transpose in registers: afterwards bit t of a[i] is what bit i of a[t] was.
+// Used by the all2all form of the scan (k_bitmap_matrix / k_scan_matrix): with the presence bitmaps of 32
+// references transposed into one 32-bit word per k-mer, ONE gather per query position answers the probe for
+// all 32 references, and a second transpose turns the 32 gathered words of a query word into the 32 hit
+// masks (one per reference) that scan_word() computes one probe at a time.
+LZ_HD void transpose32(uint32_t (&a)[32])
+{
+    uint32_t m = 0x0000FFFFu;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int s = 16; s; s >>= 1) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 32; ++k) {
+            if (k & s) continue;
+            // swap the high-s columns of row k with the low-s columns of row k+s
+            const uint32_t t = ((a[k] >> s) ^ a[k + s]) & m;
+            a[k + s] ^= t;
+            a[k] ^= t << s;
+        }
+        m ^= m << (s >> 1);          // 0x0000FFFF -> 0x00FF00FF -> 0x0F0F0F0F -> 0x33333333 -> 0x55555555
+    }
+}
+// what scan_word() masks away, for the 32 positions starting at pos0 of a query whose loop ends at `end`:
+// positions whose mal-mer covers an N, positions >= end
+LZ_HD uint32_t scan_valid_mask(const Rec& a, const Rec& b, int mal, int pos0, int end)
+{
+    uint32_t bad = 0;
+    if (a.z | b.z) {
+        const uint64_t nz = ((uint64_t)b.z << 32) | a.z;
+        uint64_t u = nz;
+        for (int j = 1; j < mal; ++j) u |= nz >> j;
+        bad = (uint32_t)u;
+    }
+    const int nv = end - pos0;
+    return ~bad & (nv >= 32 ? 0xFFFFFFFFu : (nv <= 0 ? 0u : low_mask32(nv)));
+}
 // first positions of the runs of consecutive hits inside a hit mask (a run never crosses a multiple of 8)
 LZ_HD uint32_t run_first_bits(uint32_t m) { return m & ~(m & (m << 1) & ~0x01010101u); }
 
@@ -1112,22 +1151,6 @@ LZ_HD uint32_t run_first_bits(uint32_t m) { return m & ~(m & (m << 1) & ~0x01010
 // position of the best anchor, z = w2, w = w3 (the fields of hit_probe / hit_extend / spec_first_seed).
 // (HitEntry, the hit-list element, is declared in layout.h.)
 
-// Stage C of a record: the speculative seed scan of the window the hit opens if it is taken
-// (spec_first_seed), over query positions up to lim_p (the next hit run, or the last loop position)
-template <class PT>
-LZ_HD void hit_spec(const PairView& pv, const PT& P, int p, int lim_p, uint32_t pos, uint32_t& w2, uint32_t& w3)
-{
-    const int adv = (int)(w2 & 63u) + (int)((w2 >> 6) & 63u);
-    const int si0 = p + adv, sP0 = (int)pos + adv;
-    int K = lim_p - si0;
-    if (K > P.mqd) K = P.mqd;
-    const int ks = spec_first_seed(pv, P, si0, sP0, K);
-    if (ks >= 0) {
-        w3 |= ((uint32_t)(K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
-        w2 |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;
-    }
-}
-
 // length of the run of hits that follow the run-first bit b of hit mask m (0..7)
 LZ_HD int run_following(uint32_t m, int b)
 {
@@ -1136,42 +1159,64 @@ LZ_HD int run_following(uint32_t m, int b)
     return ctz32(follow);
 }
 
-// The stored record of hit-list entry t (one thread per entry in k_hit_records).  `sync` is the
-// reconvergence point between the stages (lanes take different numbers of probe / scan iterations).
+// The stored record of hit-list entry t, stages A and B (k_hit_probe, one thread per entry): table probe,
+// match length, both approximate extensions.  `sync` is the reconvergence point between the stages
+// (lanes take different numbers of probe iterations).
 template <class PT, class SyncFn>
-LZ_HD Rec hit_record(const PairView& pv, const PT& P, int n_loop, const HitEntry* list, uint64_t t, uint64_t total,
-                     bool live, SyncFn sync)
+LZ_HD Rec hit_record_probe(const PairView& pv, const PT& P, const HitEntry* list, uint64_t t, bool live, SyncFn sync)
 {
     Rec o; o.x = 0; o.y = 0; o.z = 0; o.w = 0;
     HitEntry e; e.pair = 0; e.pr = 0;
     if (live) e = list[t];
     const int p = (int)(e.pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
-    uint32_t pos = 0, w2 = 0, w3 = 0, succ = 0;
+    uint32_t pos = 0, w2 = 0, w3 = 0;
     if (live) hit_probe(pv, P, p, pos, w2);
     w2 |= (e.pr >> HIT_ENTRY_RUN_SHIFT) << HIT_RUN_SHIFT;
     sync();
     if (live && (w2 & (HIT_LIVE | HIT_DEFER)) == HIT_LIVE) hit_extend(pv, P, p, (int)pos, w2, w3);
-    sync();
-    if (PT::kSpecSeeds && P.mqd <= SPEC_MAX_K && live && (w2 & HIT_FWD)) {
-        // scanned up to the next hit run of this pair at or after the window's start (inclusive), or the
-        // last position of the loop
-        const int si0 = p + (int)(w2 & 63u) + (int)((w2 >> 6) & 63u);
-        int lim_p = n_loop - 1;
-        bool inside = false;                 // the walk would come to stand inside a run on the way
-        for (uint64_t u = t + 1; u < total && list[u].pair == e.pair; ++u) {
-            const int pu = (int)(list[u].pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
-            if (pu >= si0) {
-                lim_p = pu;
-                if (!inside && u - t <= 7u) succ = (uint32_t)(u - t);
-                break;
-            }
-            if (pu + (int)(list[u].pr >> HIT_ENTRY_RUN_SHIFT) >= si0) inside = true;
-        }
-        hit_spec(pv, P, p, lim_p, pos, w2, w3);
-        if (!((w3 >> 18) & 63u)) succ = 0;   // no speculative seed record: the walk goes through the general code
-    }
-    o.x = (uint32_t)p | (succ << HIT_ENTRY_RUN_SHIFT); o.y = pos; o.z = w2; o.w = w3;
+    o.x = (uint32_t)p; o.y = pos; o.z = w2; o.w = w3;
     return o;
+}
+
+// Stage C (k_hit_spec): the speculative seed scan of the window the hit opens if it is taken.  The job is
+// described first (cheap: where the window starts, how far to scan, the tentative successor link) so that the
+// scans of a thread block can be dealt to its threads in order of their length (lanes of a warp then run
+// about the same number of rows), then run (spec_first_seed) and folded into the record.
+struct SpecJob { int si0, sP0, K; uint32_t succ; bool need; };
+template <class PT>
+LZ_HD SpecJob hit_spec_job(const PT& P, int n_loop, const HitEntry* list, uint64_t t, uint64_t total, const Rec& rec)
+{
+    SpecJob j; j.si0 = 0; j.sP0 = 0; j.K = -1; j.succ = 0; j.need = false;
+    if (!(PT::kSpecSeeds && P.mqd <= SPEC_MAX_K && (rec.z & HIT_FWD))) return j;
+    const int adv = (int)(rec.z & 63u) + (int)((rec.z >> 6) & 63u);
+    j.si0 = (int)rec.x + adv;
+    j.sP0 = (int)rec.y + adv;
+    // scanned up to the next hit run of this pair at or after the window's start (inclusive), or the last
+    // position of the loop
+    int lim_p = n_loop - 1;
+    bool inside = false;                 // the walk would come to stand inside a run on the way
+    const uint32_t pair = list[t].pair;
+    for (uint64_t u = t + 1; u < total && list[u].pair == pair; ++u) {
+        const int pu = (int)(list[u].pr & (uint32_t)(LZ_STAGED_MAX_POS - 1));
+        if (pu >= j.si0) {
+            lim_p = pu;
+            if (!inside && u - t <= 7u) j.succ = (uint32_t)(u - t);
+            break;
+        }
+        if (pu + (int)(list[u].pr >> HIT_ENTRY_RUN_SHIFT) >= j.si0) inside = true;
+    }
+    j.K = lim_p - j.si0;
+    if (j.K > P.mqd) j.K = P.mqd;
+    j.need = true;
+    return j;
+}
+// ks = spec_first_seed(pv, P, j.si0, j.sP0, j.K)
+LZ_HD void hit_spec_finish(Rec& rec, const SpecJob& j, int ks)
+{
+    if (ks < 0) return;              // no speculative seed record: the walk goes through the general code (no link)
+    rec.w |= ((uint32_t)(j.K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
+    rec.z |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;
+    rec.x |= j.succ << HIT_ENTRY_RUN_SHIFT;
 }
 
 // ---- successor links (k_link_records, one thread per record).  hit_record() left in x[29,32) the offset of

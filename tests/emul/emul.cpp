@@ -81,7 +81,11 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
         }
     }
     std::vector<Rec> recs(list.size() + 1);
-    for (size_t t = 0; t < list.size(); ++t) recs[t] = hit_record(pv, P, n_loop, list.data(), t, list.size(), true, [] {});
+    for (size_t t = 0; t < list.size(); ++t) recs[t] = hit_record_probe(pv, P, list.data(), t, true, [] {});      // k_hit_probe
+    for (size_t t = 0; t < list.size(); ++t) {                                                                    // k_hit_spec
+        const SpecJob j = hit_spec_job(P, n_loop, list.data(), t, list.size(), recs[t]);
+        if (j.need) hit_spec_finish(recs[t], j, spec_first_seed(pv, P, j.si0, j.sP0, j.K));
+    }
     // k_link_records: the link of every record is decided from the records as hit_record() left them
     std::vector<uint32_t> link(list.size());
     for (size_t t = 0; t < list.size(); ++t) {
@@ -236,5 +240,62 @@ extern "C" void lzani_emul_pack_records(const uint8_t* src, uint32_t len, int mr
         memcpy(r_out + 4 * i, &o, 16);
     }
 }
+// the register bit-matrix transpose of the all2all scan (parse_core.h: transpose32)
+extern "C" void lzani_emul_transpose32(uint32_t* a32)
+{
+    uint32_t a[32];
+    memcpy(a, a32, sizeof(a));
+    transpose32(a);
+    memcpy(a32, a, sizeof(a));
+}
+// the matrix form of the scan for one (reference, query) pair: hit masks of every query word, computed the
+// way k_bitmap_matrix + k_scan_matrix do (this reference in column `col` of a 32-reference block whose other
+// columns hold arbitrary bits) -- must equal scan_word().  Returns the number of differing words.
+extern "C" int lzani_emul_matrix_scan_check(const int32_t* p8, const uint8_t* ref3, uint32_t ref_len, const uint8_t* qry3,
+                                            uint32_t qry_len, int col, uint32_t noise)
+{
+    Prm P{p8[0], p8[1], p8[2], p8[3], p8[4], p8[5], p8[6], p8[7]};
+    if (2 * P.mal > 22) return -1;
+    HostSeq r, q;
+    build_seq(r, ref3, ref_len, P);
+    build_seq(q, qry3, qry_len, P);
+    HostIndex ix;
+    build_index(ix, r, P);
+    PairView pv;
+    pv.q = q.q.data(); pv.Dq = q.len + P.mrd;
+    pv.r = r.r.data(); pv.Dr = r_form_len(r.len, P.mrd);
+    pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
+    pv.table = ix.table.data(); pv.tbits = ix.tbits;
+    // k_bitmap_matrix: 32 keys per step, column `col` = this reference, the others pseudo-random
+    const uint32_t n_keys = 1u << ix.bbits;
+    std::vector<uint32_t> mc(n_keys);
+    uint32_t x = noise | 1u;
+    const uint32_t kw = n_keys / 32 ? n_keys / 32 : 1;
+    for (uint32_t t = 0; t < kw; ++t) {
+        uint32_t a[32];
+        for (int i = 0; i < 32; ++i) { x = x * 1664525u + 1013904223u; a[i] = i == col ? ix.bitmap[t] : x; }
+        transpose32(a);
+        for (int b = 0; b < 32 && 32 * t + b < n_keys; ++b) mc[32 * t + b] = a[b];
+    }
+    // k_scan_matrix
+    const int n_loop = pv.Dq - P.msl;
+    const int n_words = n_loop > 0 ? (n_loop + 31) / 32 : 0;
+    const uint32_t kmask = n_keys - 1u, km = low_mask32(P.mal);
+    int bad = 0;
+    for (int wd = 0; wd < n_words; ++wd) {
+        const Rec a = pv.q[wd], b = pv.q[wd + 1];
+        const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
+        uint32_t v[32];
+        for (int t = 0; t < 32; ++t) {
+            const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
+            v[t] = mc[((lo & km) | (hs & ~km)) & kmask];
+        }
+        transpose32(v);
+        const uint32_t m = v[col] & scan_valid_mask(a, b, P.mal, 32 * wd, n_loop);
+        if (m != scan_word(pv, P, 32 * wd, n_loop)) ++bad;
+    }
+    return bad;
+}
+
 extern "C" int lzani_emul_q_recs(uint32_t len, int mrd) { return q_form_recs((int)len, mrd); }
 extern "C" int lzani_emul_r_recs(uint32_t len, int mrd) { return r_form_recs((int)len, mrd); }

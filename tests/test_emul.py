@@ -94,3 +94,36 @@ def test_region_fold_matches_oracle_regions(emul, sname, params):
             assert a.shape == b.shape and np.array_equal(a, b), (r, q)
             total += len(b)
     assert total > 0
+
+
+def test_transpose32_is_a_bit_matrix_transpose(emul):
+    rng = np.random.default_rng(5)
+    for _ in range(20):
+        a = rng.integers(0, 1 << 32, size=32, dtype=np.uint64).astype(np.uint32)
+        bits = ((a[:, None] >> np.arange(32, dtype=np.uint32)[None, :]) & 1).astype(np.uint64)   # bits[row, col]
+        want = (bits.T << np.arange(32, dtype=np.uint64)[None, :]).sum(axis=1).astype(np.uint32)
+        got = a.copy()
+        emul.lib.lzani_emul_transpose32(got.ctypes.data)
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("params", [None, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1)])
+def test_matrix_scan_equals_probe_scan(emul, params):
+    """all2all form of the scan (bitmaps of 32 references transposed into one word per k-mer, one gather per
+    query position, transpose back) against scan_word(), incl. N runs and the end of the loop."""
+    ss = mg.get_set("edge")
+    names, seqs = synth.families(1, 3, 2000, 3000, seed=9)
+    ss2 = hostio.SeqSet(names, seqs)
+    p8 = hostio.params_array(params)
+    checked = 0
+    for s_ in (ss, ss2):
+        n = len(s_)
+        for r in range(n):
+            for q in range(n):
+                if r == q:
+                    continue
+                bad = emul.lib.lzani_emul_matrix_scan_check(p8.ctypes.data, s_.packed[r].ctypes.data, int(s_.lens[r]),
+                                                            s_.packed[q].ctypes.data, int(s_.lens[q]), (r * 7 + q) % 32, r * 131 + q)
+                assert bad == 0, (r, q, bad)
+                checked += 1
+    assert checked > 20
