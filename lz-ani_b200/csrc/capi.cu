@@ -219,6 +219,8 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
     if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
+    // fewer resident walk blocks leave registers for the other slot's data-parallel stages to run beside the walk
+    if (const char* e = getenv("LZANI_WALK_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->walk_blocks_per_sm) c->walk_blocks_per_sm = v; }
     if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) c->staged_words = (uint64_t)v; }
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));

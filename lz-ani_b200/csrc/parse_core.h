@@ -229,6 +229,19 @@ LZ_COLD int both_ways_best(W& w, const PairView& pv, int qe, int r_left, int r_r
     const int rmax = span < r_right ? span : r_right;
     FwdStream L{&pv, q0, r_left};
     BwdStream R{&pv, qe, r_right};
+    if (span < 32) {
+        // the usual gap (a few literals before a close seed): both sides are one word, every lane loads the
+        // same two words and lane s evaluates split s
+        const uint32_t e_l = ~L.word(0) & low_mask32(span), e_r = ~R.word(0) & low_mask32(rmax);
+        typename W::template Lanes<int> v;
+        LZ_EACH(w, ln)
+        {
+            const int s = ln > span ? span : ln;
+            const int u = span - s;
+            v[ln] = popc32(e_l & low_mask32(s)) + (u > rmax ? 0 : popc32(e_r & low_mask32(u)));
+        }
+        return w.max_i32(v);
+    }
     typename W::template Lanes<uint32_t> el, er;   // EQUAL bits of the two sides, per word
     typename W::template Lanes<int> cl, cr, pl, pr;
     LZ_EACH(w, ln)
@@ -1362,6 +1375,11 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                     }
                 }
                 const uint32_t left = bs.n - cur;
+                LZ_EACH(w, ln)
+                {
+                    // the next batch: 32 records = four 128-byte lines, most likely still in HBM
+                    if (ln < 4 && 32u + 8u * (uint32_t)ln < left) w.prefetch(bs.recs + cur + 32u + 8u * (uint32_t)ln);
+                }
                 b_loaded = left < 32u ? (int)left : 32;
                 b_cover = left > 32u ? w.get(r_p, 31) + (int)((w.get(r_w2, 31) >> HIT_RUN_SHIFT) & 7u) + 1 : n_loop;
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)

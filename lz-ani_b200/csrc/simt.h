@@ -131,6 +131,8 @@ struct DevWarp {
     }
     // orders this warp's shared-memory scratch writes before its later reads
     __device__ __forceinline__ void sync() const { __syncwarp(); }
+    // hint: the line at p will be read soon
+    __device__ __forceinline__ void prefetch(const void* p) const { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
     // value of lane `src` (uniform src)
     template <class T>
     __device__ __forceinline__ T get(const Lanes<T>& x, int src) const { return __shfl_sync(0xFFFFFFFFu, x.v, src); }
@@ -187,6 +189,7 @@ struct HostWarp {
     uint32_t or_u32(const Lanes<uint32_t>& x) const { uint32_t r = 0; for (int l = 0; l < 32; ++l) r |= x.v[l]; return r; }
     uint64_t or_u64(const Lanes<uint64_t>& x) const { uint64_t r = 0; for (int l = 0; l < 32; ++l) r |= x.v[l]; return r; }
     void sync() const {}
+    void prefetch(const void*) const {}
     template <class T>
     T get(const Lanes<T>& x, int src) const { return x.v[src & 31]; }
     template <class T>
