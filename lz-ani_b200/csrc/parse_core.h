@@ -629,6 +629,14 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
     r.c = x.c | (y.c >> j);
     return r;
 }
+LZ_HD V3 v3_and_shr(const V3& x, const V3& y, int j)  // x & (y >> j), 0 < j < 32, zeros shifted in
+{
+    V3 r;
+    r.a = x.a & funnel_r(y.a, y.b, j);
+    r.b = x.b & funnel_r(y.b, y.c, j);
+    r.c = x.c & (y.c >> j);
+    return r;
+}
 constexpr int SPEC_MAX_K = 57;
 constexpr int SPEC_MULTI = 1 << 15;
 #ifndef LZ_CHAIN
@@ -672,43 +680,44 @@ LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K
         if (n0 | (nr > 32 ? (n1 & low_mask32(nr - 32 > 32 ? 32 : nr - 32)) : 0u) | (nr > 64 ? (n2 & low_mask32(nr - 64)) : 0u)) return -1;
     }
     uint64_t ql = ((uint64_t)Q.lo1 << 32) | Q.lo0, qh = ((uint64_t)Q.hi1 << 32) | Q.hi0;
-    // valid reference positions of row k: x < k + mrd (mask grows by one bit per row)
-    const int n0 = P.mrd;
-    uint32_t m0 = low_mask32(n0 > 32 ? 32 : n0), m1 = n0 > 32 ? low_mask32(n0 - 32 > 32 ? 32 : n0 - 32) : 0u,
-             m2 = n0 > 64 ? low_mask32(n0 - 64) : 0u;
-    V3 mis_prev{0, 0, 0}, a2[4], a4[4];
+    // MATCH masks E_m (bit x: r[P0+x] == q[i0+m]), AND-combined by doubling: pairs A2, fours A4, sevens S.
+    // Shifted-in zeros and rows that do not exist read as "no match", so nothing has to be masked inside the
+    // loop: the validity of a candidate (reference offset x < k + mrd, position k <= K) is tested only when one
+    // appears (about 1 row in 100).  Rows are run in groups of four; up to three rows past the last one are
+    // evaluated for nothing (they can only produce candidates at k > K, which are dropped).
+    V3 e_prev{0, 0, 0}, a2[4], a4[4];
     for (int u = 0; u < 4; ++u) a2[u] = a4[u] = V3{0, 0, 0};
     const int m_last = K + 6;
     for (int mb = 0; mb <= m_last; mb += 4) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int u = 0; u < 4; ++u) {      // ring slots (m mod 4) are compile-time; body kept small (I-cache)
+        for (int u = 0; u < 4; ++u) {      // ring slots (m mod 4) are compile-time
             const int m = mb + u;
-            if (m > m_last) return 64;
-            // Mis_m: reference window against query base m
-            const uint32_t bl = 0u - ((uint32_t)(ql >> u) & 1u), bh = 0u - ((uint32_t)(qh >> u) & 1u);
-            V3 mis;
-            mis.a = (rl.a ^ bl) | (rh.a ^ bh);
-            mis.b = (rl.b ^ bl) | (rh.b ^ bh);
-            mis.c = (rl.c ^ bl) | (rh.c ^ bh);
-            // pairs: A2_{m-1}; fours: A4_{m-3}; sevens: S_{m-6}
-            const V3 p2 = v3_or_shr(mis_prev, mis, 1);              // A2_{m-1}
-            const V3 p4 = v3_or_shr(a2[(u + 1) % 4], p2, 2);        // A4_{m-3} = A2_{m-3} | A2_{m-1}>>2
-            const V3 s7 = v3_or_shr(a4[(u + 2) % 4], p4, 3);        // S_{m-6}  = A4_{m-6} | A4_{m-3}>>3
+            // all-ones where the query base's plane bit is 0: equal <=> (r ^ ~q) on both planes
+            const uint32_t nl = ((uint32_t)(ql >> u) & 1u) - 1u, nh = ((uint32_t)(qh >> u) & 1u) - 1u;
+            V3 eq;
+            eq.a = (rl.a ^ nl) & (rh.a ^ nh);
+            eq.b = (rl.b ^ nl) & (rh.b ^ nh);
+            eq.c = (rl.c ^ nl) & (rh.c ^ nh);
+            const V3 p2 = v3_and_shr(e_prev, eq, 1);                // A2_{m-1} = E_{m-1} & E_m>>1
+            const V3 p4 = v3_and_shr(a2[(u + 1) % 4], p2, 2);       // A4_{m-3} = A2_{m-3} & A2_{m-1}>>2
+            const V3 s7 = v3_and_shr(a4[(u + 2) % 4], p4, 3);       // S_{m-6}  = A4_{m-6} & A4_{m-3}>>3
             a2[(u + 3) % 4] = p2;                                   // slot (m-1) mod 4
             a4[(u + 1) % 4] = p4;                                   // slot (m-3) mod 4
-            mis_prev = mis;
-            if (m >= 6) {
-                const uint32_t c0 = ~s7.a & m0, c1 = ~s7.b & m1, c2 = ~s7.c & m2;
+            e_prev = eq;
+            if ((s7.a | s7.b | s7.c) && m >= 6) {
+                const int k = m - 6;
+                const int nv = k + P.mrd;                           // valid reference offsets of row k: x < k + mrd
+                const uint32_t c0 = s7.a & low_mask32(nv > 32 ? 32 : nv);
+                const uint32_t c1 = nv > 32 ? s7.b & low_mask32(nv - 32 > 32 ? 32 : nv - 32) : 0u;
+                const uint32_t c2 = nv > 64 ? s7.c & low_mask32(nv - 64 > 32 ? 32 : nv - 64) : 0u;
                 if (c0 | c1 | c2) {
+                    if (k > K) return 64;
                     const int x = c0 ? ctz32(c0) : (c1 ? 32 + ctz32(c1) : 64 + ctz32(c2));
                     const bool multi = popc32(c0) + popc32(c1) + popc32(c2) > 1;
-                    return (m - 6) | (x << 8) | (multi ? SPEC_MULTI : 0);
+                    return k | (x << 8) | (multi ? SPEC_MULTI : 0);
                 }
-                m2 = (m2 << 1) | (m1 >> 31);
-                m1 = (m1 << 1) | (m0 >> 31);
-                m0 = (m0 << 1) | 1u;
             }
         }
         ql >>= 4;
