@@ -81,7 +81,7 @@ typedef struct lzani_timing_t {
     double h2d_ms;      /* pair list (+ sequences if not yet resident) host->device */
     double pack_ms;     /* K1: base-6 triples -> bit-plane records               */
     double index_ms;    /* K2: anchor presence bitmap + anchor table build        */
-    double parse_ms;    /* K3: warp-per-pair parse                                */
+    double parse_ms;    /* K3: the parse stage (staged kernels + warp-per-pair walk) */
     double d2h_ms;      /* results device->host                                   */
     double total_ms;    /* first event to last event                              */
     uint64_t n_pairs;   /* ordered pairs processed                                */
