@@ -656,13 +656,10 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
     } else if (n_words) {
         e = with_prm(P, [&](auto PT) {
             using K = decltype(PT);
-            static bool attr_set = false;      // per instantiation
             const size_t smem = sizeof(uint32_t) << (LZ_COARSE_BITS - 5);
-            if (!attr_set) {
-                cudaError_t ea = cudaFuncSetAttribute(k_scan_hits<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-                if (ea != cudaSuccess) return ea;
-                attr_set = true;
-            }
+            // per device (a process may drive several GPUs, one context each): set on every launch
+            cudaError_t ea = cudaFuncSetAttribute(k_scan_hits<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (ea != cudaSuccess) return ea;
             k_scan_hits<K><<<scan_blocks, LZ_SCAN_THREADS, smem, st>>>(recs, B.desc, B.word_off, n_pairs, PT, bitmap_pool, B.hm, B.wpair);
             return cudaGetLastError();
         });
