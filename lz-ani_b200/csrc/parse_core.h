@@ -629,12 +629,13 @@ LZ_HD V3 v3_or_shr(const V3& x, const V3& y, int j)   // x | (y >> j), 0 < j < 3
     r.c = x.c | (y.c >> j);
     return r;
 }
-LZ_HD V3 v3_and_shr(const V3& x, const V3& y, int j)  // x & (y >> j), 0 < j < 32, zeros shifted in
+template <int NW>
+LZ_HD V3 v3_and_shr(const V3& x, const V3& y, int j)  // x & (y >> j) on the first NW words, 0 < j < 32, zeros shifted in
 {
     V3 r;
     r.a = x.a & funnel_r(y.a, y.b, j);
-    r.b = x.b & funnel_r(y.b, y.c, j);
-    r.c = x.c & (y.c >> j);
+    r.b = NW > 2 ? x.b & funnel_r(y.b, y.c, j) : x.b & (y.b >> j);
+    r.c = NW > 2 ? x.c & (y.c >> j) : 0u;
     return r;
 }
 constexpr int SPEC_MAX_K = 57;
@@ -661,6 +662,46 @@ struct WarpScratch {
 #if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
 static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batches = 0, lz_hits = 0, lz_matches = 0, lz_fast = 0, lz_chain = 0, lz_why[12] = {0};   // TEST ONLY counters (tests/emul)
 #endif
+// four rows of the speculative seed scan (spec_first_seed below) on the first NW words of the window
+constexpr int SPEC_GO_ON = -2;
+template <int NW, class PT>
+LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, uint64_t ql, uint64_t qh, int mb, int K, V3& e_prev,
+                     V3 (&a2)[4], V3 (&a4)[4])
+{
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int u = 0; u < 4; ++u) {      // ring slots (m mod 4) are compile-time
+        const int m = mb + u;
+        // all-ones where the query base's plane bit is 0: equal <=> (r ^ ~q) on both planes
+        const uint32_t nl = ((uint32_t)(ql >> u) & 1u) - 1u, nh = ((uint32_t)(qh >> u) & 1u) - 1u;
+        V3 eq;
+        eq.a = (rl.a ^ nl) & (rh.a ^ nh);
+        eq.b = (rl.b ^ nl) & (rh.b ^ nh);
+        eq.c = NW > 2 ? (rl.c ^ nl) & (rh.c ^ nh) : 0u;
+        const V3 p2 = v3_and_shr<NW>(e_prev, eq, 1);                // A2_{m-1} = E_{m-1} & E_m>>1
+        const V3 p4 = v3_and_shr<NW>(a2[(u + 1) % 4], p2, 2);       // A4_{m-3} = A2_{m-3} & A2_{m-1}>>2
+        const V3 s7 = v3_and_shr<NW>(a4[(u + 2) % 4], p4, 3);       // S_{m-6}  = A4_{m-6} & A4_{m-3}>>3
+        a2[(u + 3) % 4] = p2;                                       // slot (m-1) mod 4
+        a4[(u + 1) % 4] = p4;                                       // slot (m-3) mod 4
+        e_prev = eq;
+        if ((s7.a | s7.b | s7.c) && m >= 6) {
+            const int k = m - 6;
+            const int nv = k + P.mrd;                               // valid reference offsets of row k: x < k + mrd
+            const uint32_t c0 = s7.a & low_mask32(nv > 32 ? 32 : nv);
+            const uint32_t c1 = nv > 32 ? s7.b & low_mask32(nv - 32 > 32 ? 32 : nv - 32) : 0u;
+            const uint32_t c2 = nv > 64 ? s7.c & low_mask32(nv - 64 > 32 ? 32 : nv - 64) : 0u;
+            if (c0 | c1 | c2) {
+                if (k > K) return 64;
+                const int x = c0 ? ctz32(c0) : (c1 ? 32 + ctz32(c1) : 64 + ctz32(c2));
+                const bool multi = popc32(c0) + popc32(c1) + popc32(c2) > 1;
+                return k | (x << 8) | (multi ? SPEC_MULTI : 0);
+            }
+        }
+    }
+    return SPEC_GO_ON;
+}
+
 template <class PT>
 LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
 {
@@ -685,41 +726,23 @@ LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K
     // loop: the validity of a candidate (reference offset x < k + mrd, position k <= K) is tested only when one
     // appears (about 1 row in 100).  Rows are run in groups of four; up to three rows past the last one are
     // evaluated for nothing (they can only produce candidates at k > K, which are dropped).
+    // The third window word (offsets 64..95) only matters for rows k with k + mrd + 6 > 64: the first rows
+    // run on two words.
     V3 e_prev{0, 0, 0}, a2[4], a4[4];
     for (int u = 0; u < 4; ++u) a2[u] = a4[u] = V3{0, 0, 0};
     const int m_last = K + 6;
-    for (int mb = 0; mb <= m_last; mb += 4) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-        for (int u = 0; u < 4; ++u) {      // ring slots (m mod 4) are compile-time
-            const int m = mb + u;
-            // all-ones where the query base's plane bit is 0: equal <=> (r ^ ~q) on both planes
-            const uint32_t nl = ((uint32_t)(ql >> u) & 1u) - 1u, nh = ((uint32_t)(qh >> u) & 1u) - 1u;
-            V3 eq;
-            eq.a = (rl.a ^ nl) & (rh.a ^ nh);
-            eq.b = (rl.b ^ nl) & (rh.b ^ nh);
-            eq.c = (rl.c ^ nl) & (rh.c ^ nh);
-            const V3 p2 = v3_and_shr(e_prev, eq, 1);                // A2_{m-1} = E_{m-1} & E_m>>1
-            const V3 p4 = v3_and_shr(a2[(u + 1) % 4], p2, 2);       // A4_{m-3} = A2_{m-3} & A2_{m-1}>>2
-            const V3 s7 = v3_and_shr(a4[(u + 2) % 4], p4, 3);       // S_{m-6}  = A4_{m-6} & A4_{m-3}>>3
-            a2[(u + 3) % 4] = p2;                                   // slot (m-1) mod 4
-            a4[(u + 1) % 4] = p4;                                   // slot (m-3) mod 4
-            e_prev = eq;
-            if ((s7.a | s7.b | s7.c) && m >= 6) {
-                const int k = m - 6;
-                const int nv = k + P.mrd;                           // valid reference offsets of row k: x < k + mrd
-                const uint32_t c0 = s7.a & low_mask32(nv > 32 ? 32 : nv);
-                const uint32_t c1 = nv > 32 ? s7.b & low_mask32(nv - 32 > 32 ? 32 : nv - 32) : 0u;
-                const uint32_t c2 = nv > 64 ? s7.c & low_mask32(nv - 64 > 32 ? 32 : nv - 64) : 0u;
-                if (c0 | c1 | c2) {
-                    if (k > K) return 64;
-                    const int x = c0 ? ctz32(c0) : (c1 ? 32 + ctz32(c1) : 64 + ctz32(c2));
-                    const bool multi = popc32(c0) + popc32(c1) + popc32(c2) > 1;
-                    return k | (x << 8) | (multi ? SPEC_MULTI : 0);
-                }
-            }
-        }
+    int m_two = 58 - P.mrd;                 // rows below this (rounded down to a group) need two words
+    m_two = m_two > 0 ? m_two & ~3 : 0;
+    int mb = 0;
+    for (; mb < m_two && mb <= m_last; mb += 4) {
+        const int r = spec_rows4<2>(P, rl, rh, ql, qh, mb, K, e_prev, a2, a4);
+        if (r != SPEC_GO_ON) return r;
+        ql >>= 4;
+        qh >>= 4;
+    }
+    for (; mb <= m_last; mb += 4) {
+        const int r = spec_rows4<3>(P, rl, rh, ql, qh, mb, K, e_prev, a2, a4);
+        if (r != SPEC_GO_ON) return r;
         ql >>= 4;
         qh >>= 4;
     }
