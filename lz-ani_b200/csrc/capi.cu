@@ -77,6 +77,7 @@ struct lzani_ctx {
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
     uint64_t staged_words = 96ull << 20;  // words per chunk (LZANI_STAGED_WORDS)
+    uint64_t staged_recs = 0;             // record capacity per chunk (LZANI_STAGED_RECS; 0: 1.25 per word)
     int walk_blocks_per_sm = 1;
     double rec_per_word = 1.0;            // observed hit runs per 32 query positions (chunk sizing)
     uint32_t staged_chunks = 0;           // of the last run
@@ -218,6 +219,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
     c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
     if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
+    if (const char* e = getenv("LZANI_STAGED_RECS")) { const long long v = atoll(e); if (v > 0) c->staged_recs = (uint64_t)v; }
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
     // fewer resident walk blocks leave registers for the other slot's data-parallel stages to run beside the walk
     if (const char* e = getenv("LZANI_WALK_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->walk_blocks_per_sm) c->walk_blocks_per_sm = v; }
@@ -478,7 +480,8 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         else for (uint32_t j = 0; j < n_rows; ++j) words_run += words_all - wq[row_ref[j]];
         const uint64_t wcap = std::max<uint64_t>(std::min<uint64_t>(c->staged_words, words_run), std::max<uint32_t>(words_max, 1u));
         const uint64_t pcap = std::min<uint64_t>(n_pairs, (uint64_t)1 << 19);
-        const uint64_t rcap = wcap + wcap / 4 + 1024;
+        uint64_t rcap = wcap + wcap / 4 + 1024;
+        if (c->staged_recs) rcap = c->staged_recs;       // test knob: forces the chunk-halving / growth paths
         const int n_slots = words_run > wcap ? 2 : 1;
         for (int i = 0; i < n_slots; ++i) {
             lzani_ctx::Slot& sl = c->slot[i];

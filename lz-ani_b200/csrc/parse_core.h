@@ -643,6 +643,17 @@ constexpr int SPEC_MULTI = 1 << 15;
 #ifndef LZ_CHAIN
 #define LZ_CHAIN 0
 #endif
+// rounds of the diagonal seed scan (32 diagonals each) issued together: their loads overlap
+#ifndef LZ_DIAG_UNROLL
+#define LZ_DIAG_UNROLL 1
+#endif
+#if defined(__CUDACC__)
+#define LZ_PRAGMA_(x) _Pragma(#x)
+#define LZ_PRAGMA(x) LZ_PRAGMA_(x)
+#define LZ_DIAG_LOOP LZ_PRAGMA(unroll LZ_DIAG_UNROLL)
+#else
+#define LZ_DIAG_LOOP
+#endif
 constexpr bool kChain = LZ_CHAIN != 0;   // successor links (measured slower on B200: off)
 #ifndef LZ_SCAN_UNROLL
 #define LZ_SCAN_UNROLL 4
@@ -930,7 +941,7 @@ LZ_COLD uint64_t diag_seed_starts(W& w, const PairView& pv, const PT& P, const P
 {
     typename W::template Lanes<uint64_t> sm;
     LZ_EACH(w, ln) sm[ln] = 0;
-    LZ_ROLLED
+    LZ_DIAG_LOOP
     for (int dbase = d_lo; dbase < d_hi; dbase += 32) {
         LZ_EACH(w, ln)
         {

@@ -196,3 +196,40 @@ def test_region_records_match_oracle(sname, params):
         assert total == len(regs) and total > 0
     finally:
         m.close()
+
+
+@pytest.mark.parametrize("env", [
+    dict(LZANI_STAGED_WORDS="300"),                                  # many chunks, rows cut in the middle (probe scan for those)
+    dict(LZANI_STAGED_WORDS="300", LZANI_STAGED_RECS="40"),          # records overflow: chunks halved, single pairs grow the buffers
+    dict(LZANI_STAGED_WORDS="20000", LZANI_MATRIX_SCAN="0"),         # probe scan with the folded bitmap in shared memory
+    dict(LZANI_STAGED="0"),                                          # one-kernel form
+])
+def test_staged_chunking_paths(env, monkeypatch):
+    """The host side of the staged parse under hostile capacities: chunk boundaries inside rows, record
+    buffers that overflow (halving, growth), both scan kernels, dense and sparse lists -- same integers."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    for case in ("synth_small_default", "edge_default", "example_default"):
+        if case not in mg.CASES:
+            continue
+        sname, params = mg.CASES[case]
+        ss = mg.get_set(sname)
+        got, t = run_gpu(ss, params)
+        assert np.array_equal(got, GOLD[case]), (env, case)
+    # sparse list (probe scan): every third pair of the example set
+    sname, params = mg.CASES["example_default"]
+    ss = mg.get_set(sname)
+    n = len(ss)
+    rows, off, q = [], [0], []
+    for r in range(n):
+        qs = [x for x in range(n) if x != r and (x + r) % 3 == 0]
+        rows.append(r); q.extend(qs); off.append(len(q))
+    m = lz.Matcher(params=params, device=0)
+    try:
+        m.set_sequences(ss)
+        got = m.run_rows(np.array(rows, dtype=np.uint32), np.array(off, dtype=np.uint64), np.array(q, dtype=np.uint32))
+    finally:
+        m.close()
+    full = GOLD["example_default"].reshape(n, n - 1, 3)
+    want = np.array([full[r, x if x < r else x - 1] for r in range(n) for x in range(n) if x != r and (x + r) % 3 == 0])
+    assert np.array_equal(got, want), env
