@@ -76,7 +76,7 @@ struct lzani_ctx {
     } slot[2];
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
-    uint64_t staged_words = 96ull << 20;  // words per chunk (LZANI_STAGED_WORDS)
+    uint64_t staged_words = 0;            // words per chunk (LZANI_STAGED_WORDS; 0: sized from the free HBM at the first run)
     uint64_t staged_recs = 0;             // record capacity per chunk (LZANI_STAGED_RECS; 0: 1.25 per word)
     int walk_blocks_per_sm = 1;
     double rec_per_word = 1.0;            // observed hit runs per 32 query positions (chunk sizing)
@@ -474,6 +474,16 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
             words_all += wq[i];
             words_max = std::max(words_max, wq[i]);
         }
+    }
+    if (staged && !c->staged_words) {
+        // chunk size: both slots together may take a fifth of the free HBM (~40 B of scratch per query word),
+        // between 96 M and 768 M words -- large chunks keep many rows together (the all2all scan handles 32
+        // references per gather) and the walk's tails rare; buffers still only grow to what a run needs
+        size_t fr = 0, tot = 0;
+        LZ_CUDA(c, cudaMemGetInfo(&fr, &tot));
+        uint64_t wds = (uint64_t)((double)fr * 0.2 / 80.0);
+        wds = std::max<uint64_t>(96ull << 20, std::min<uint64_t>(wds, 768ull << 20));
+        c->staged_words = wds;
     }
     if (staged) {
         if (q_ids) for (uint64_t k = 0; k < n_pairs; ++k) words_run += wq[q_src[k]];

@@ -1366,7 +1366,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
     for (;;) {
         const int i0 = s.i;
         // the match this step finds, if any (one take_match call site keeps the code small)
-        bool matched = false;
+        bool matched = false, seed_cut = false;
         int m_qi = 0, m_lit = 0, m_pred = -1, m_pos = 0, m_len = 0;
         uint32_t m_w2 = 0, m_w3 = 0;
         int m_j = -1;                  // batch record the match was taken from (when m_w2 != 0)
@@ -1654,6 +1654,30 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 else lz_why[7]++;          // close anchor
             }
 #endif
+            // ---- SEED SHORT CUT.  Prediction on, the record of the match just taken names the first seed of its
+            // window (position sks, the only one there: reference offset spec_x) and no anchor event lies at or
+            // before it: the step the general code below would take is exactly that seed match
+            // (parser.cpp:548-580, no arbitration), so measure it and go straight to take_match().
+            if (BS::kStored && !plain && !expired && s.pred >= 0 && s.lit == 0 && sks < 64 && spec_x >= 0 && qi - i0 > sks) {
+                const int sq = i0 + sks, sp = s.pred + spec_x;
+                const uint32_t m0 = mism32(pv.q, pv.Dq, sq, pv.r, pv.Dr, sp);
+                const int sl = m0 ? ctz32(m0) : equal_len_coop(w, pv, sq, sp, 32);
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+                {   // TEST ONLY (tests/emul): the general code's answer for this step
+                    const Planes64 Qc = ext64(pv.q, i0);
+                    int cp = 0, cl = 0;
+                    uint64_t chk = 0;
+                    for (int d = -sks; d < P.mrd; ++d) chk |= run_starts(diag_equal64(pv, Qc, i0, s.pred, d), P.msl);
+                    best_seed(w, pv, P, Qc, i0, s.pred, 0, sks, -sks, P.mrd, cp, cl);
+                    const Event e2 = next_event(w, r_p, r_pos, r_w2, r_w3, i0, i0 + sks + 1, true);
+                    if ((chk & low_mask64(sks + 1)) != (1ull << sks) || cp != sp || cl != sl || e2.j >= 0 || sl < P.msl) lz_spec_mismatches++;
+                    lz_why[10]++;
+                }
+#endif
+                matched = true;
+                seed_cut = true;
+                m_qi = sq; m_lit = sks; m_pred = s.pred + sks; m_pos = sp; m_len = sl; m_w2 = 0; m_w3 = 0; m_j = -1;
+            }
             if (plain) {
                 const uint32_t w3 = ev.w3;
                 const bool keep = s.rs >= 0 && s.re - s.rs >= P.reg;
@@ -1772,7 +1796,9 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
         else lz_why[9]++;                  // no speculative record for this state
 #endif
 
-        if (s.pred < 0) {
+        if (seed_cut) {
+            // the match was found above
+        } else if (s.pred < 0) {
             // ---- no prediction (:507-532): the next event is the next live anchor record
             const Event ev = next_event(w, r_p, r_pos, r_w2, r_w3, i0, 0x7FFFFFFF, false);
             if (ev.j < 0) {

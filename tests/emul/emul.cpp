@@ -162,6 +162,7 @@ extern "C" void lzani_emul_counters(long* c)
     c[0] = lz_pred_steps; c[1] = lz_batches; c[2] = lz_hits; c[3] = lz_matches; c[4] = lz_spec_used; c[5] = lz_fast;
     for (int i = 0; i < 10; ++i) c[6 + i] = lz_why[i];
     c[16] = lz_chain;
+    c[17] = lz_why[10];      // seed short cuts
 }
 extern "C" void lzani_emul_spec_stats(long* used, long* mismatches)
 {

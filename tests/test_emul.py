@@ -60,6 +60,10 @@ def test_speculative_seed_records_agree_with_diagonal_scan(emul):
     emul.lib.lzani_emul_spec_stats(C.byref(used), C.byref(bad))
     assert used.value > 1000, "speculative records were not exercised"
     assert bad.value == 0
+    c = (C.c_long * 20)()
+    emul.lib.lzani_emul_counters(c)
+    if c[1] and c[16] + c[17]:          # staged form: links and seed short cuts were replayed against the serial rules
+        assert c[16] > 1000 and c[17] > 50, (c[16], c[17])
 
 
 @pytest.mark.parametrize("seed", list(range(100, 112)))
