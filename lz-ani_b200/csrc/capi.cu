@@ -656,7 +656,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     LZ_CUDA(c, cudaMemcpyAsync(sl.h_total, sl.B.rec_off + ch.words, sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.st));
                     LZ_CUDA(c, cudaStreamSynchronize(sl.st));
                     const uint64_t n_hit = *sl.h_total;
-                    T.launches += 2;
+                    T.launches += 1 + (ch.words ? (use_mx ? 2 * ((mx.n_rows_chunk + 31) / 32) : 1) : 0);     // our kernels (CUB's scans not counted)
                     if (ch.words) {
                         const double ratio = (double)n_hit / (double)ch.words;
                         c->rec_per_word = ratio > c->rec_per_word ? ratio : 0.5 * (c->rec_per_word + ratio);
@@ -674,7 +674,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     }
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
                                                   c->d_bitmap, c->d_table, c->d_out));
-                    T.launches += 5;
+                    T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 3 : 2) : 0);
                     ++c->staged_chunks;
                 }
                 for (auto& sl : c->slot) {
