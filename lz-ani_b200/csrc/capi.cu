@@ -34,6 +34,8 @@ struct lzani_ctx {
     SeqMeta* d_meta = nullptr;
     uint64_t* d_rec_base = nullptr;
     Rec* d_recs = nullptr;
+    uint64_t src_cap = 0, meta_cap = 0, recs_cap = 0;     // capacities: buffers are re-used by the next set_sequences
+    uint8_t* h_src = nullptr; uint64_t h_src_cap = 0;     // pinned staging of the reservoir bytes
     double pack_ms = 0;          // of the last set_sequences
     uint64_t seq_h2d_bytes = 0;
 
@@ -118,6 +120,8 @@ void free_sequences(lzani_ctx* c)
     cudaFree(c->d_meta); c->d_meta = nullptr;
     cudaFree(c->d_rec_base); c->d_rec_base = nullptr;
     cudaFree(c->d_recs); c->d_recs = nullptr;
+    if (c->h_src) { cudaFreeHost(c->h_src); c->h_src = nullptr; }
+    c->src_cap = c->meta_cap = c->recs_cap = c->h_src_cap = 0;
     c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
     c->last_valid = false;
 }
@@ -299,7 +303,9 @@ int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, con
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
     if (n && (!data || !len)) return fail(c, LZANI_ERR_ARG, "data/len == NULL");
     LZ_CUDA(c, cudaSetDevice(c->device));
-    free_sequences(c);
+    // the previous set is gone from here on (its buffers are re-used when large enough)
+    c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
+    c->last_valid = false;
     const Prm& P = c->P;
     std::vector<SeqMeta> meta(n);
     std::vector<uint64_t> rec_base((size_t)n + 1, 0);
@@ -321,8 +327,12 @@ int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, con
     rec_base[n] = recs;
 
     // stage the reservoir bytes contiguously in pinned memory, one H2D copy
-    uint8_t* h_src = nullptr;
-    LZ_CUDA(c, cudaMallocHost((void**)&h_src, src_bytes ? src_bytes : 1));
+    if (src_bytes > c->h_src_cap || !c->h_src) {
+        if (c->h_src) { cudaFreeHost(c->h_src); c->h_src = nullptr; c->h_src_cap = 0; }
+        LZ_CUDA(c, cudaMallocHost((void**)&c->h_src, src_bytes ? src_bytes : 1));
+        c->h_src_cap = src_bytes;
+    }
+    uint8_t* h_src = c->h_src;
     for (uint32_t i = 0; i < n; ++i)
         if (len[i]) memcpy(h_src + meta[i].src_off, data[i], ascii ? (size_t)len[i] : ((size_t)len[i] + 2) / 3);
 
@@ -330,10 +340,22 @@ int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, con
     do {
         cudaError_t e;
 #define LZ_TRY(call) if ((e = (call)) != cudaSuccess) { rc = fail(c, e == cudaErrorMemoryAllocation ? LZANI_ERR_NOMEM : LZANI_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e)); break; }
-        LZ_TRY(cudaMalloc((void**)&c->d_src, src_bytes ? src_bytes : 1));
-        LZ_TRY(cudaMalloc((void**)&c->d_meta, sizeof(SeqMeta) * (n ? n : 1)));
-        LZ_TRY(cudaMalloc((void**)&c->d_rec_base, sizeof(uint64_t) * ((size_t)n + 1)));
-        LZ_TRY(cudaMalloc((void**)&c->d_recs, sizeof(Rec) * (recs ? recs : 1)));
+        if (!c->d_src || src_bytes > c->src_cap) {
+            cudaFree(c->d_src); c->d_src = nullptr; c->src_cap = 0;
+            LZ_TRY(cudaMalloc((void**)&c->d_src, src_bytes ? src_bytes : 1));
+            c->src_cap = src_bytes;
+        }
+        if (!c->d_meta || !c->d_rec_base || n > c->meta_cap) {
+            cudaFree(c->d_meta); cudaFree(c->d_rec_base); c->d_meta = nullptr; c->d_rec_base = nullptr; c->meta_cap = 0;
+            LZ_TRY(cudaMalloc((void**)&c->d_meta, sizeof(SeqMeta) * (n ? n : 1)));
+            LZ_TRY(cudaMalloc((void**)&c->d_rec_base, sizeof(uint64_t) * ((size_t)n + 1)));
+            c->meta_cap = n;
+        }
+        if (!c->d_recs || recs > c->recs_cap) {
+            cudaFree(c->d_recs); c->d_recs = nullptr; c->recs_cap = 0;
+            LZ_TRY(cudaMalloc((void**)&c->d_recs, sizeof(Rec) * (recs ? recs : 1)));
+            c->recs_cap = recs;
+        }
         LZ_TRY(cudaEventRecord(c->ev[0], c->stream));
         LZ_TRY(cudaMemcpyAsync(c->d_src, h_src, src_bytes, cudaMemcpyHostToDevice, c->stream));
         LZ_TRY(cudaMemcpyAsync(c->d_meta, meta.data(), sizeof(SeqMeta) * n, cudaMemcpyHostToDevice, c->stream));
@@ -344,7 +366,6 @@ int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, con
         LZ_TRY(cudaStreamSynchronize(c->stream));
 #undef LZ_TRY
     } while (0);
-    cudaFreeHost(h_src);
     if (rc != LZANI_OK) { free_sequences(c); return rc; }
     c->n_seqs = n;
     c->n_recs = recs;
