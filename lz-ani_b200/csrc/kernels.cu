@@ -360,10 +360,12 @@ k_hit_probe(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, con
     if (live) reinterpret_cast<uint4*>(out)[t] = make_uint4(o.x, o.y, o.z, o.w);
 }
 
-// S3b.  The speculative seed scans (instruction-bound: ~40 instructions per row, up to mqd+7 rows).  The
-// scan length K differs from record to record (it ends at the next hit run), so the jobs of a thread block
-// are counting-sorted by K through shared memory and dealt out longest first: the lanes of a warp then
-// run about the same number of rows.
+// S3b.  The speculative seed scans (ALU-bound: ~33 instructions per row, up to mqd+7 rows).  The scan
+// length K differs from record to record (it ends at the next hit run), so the jobs of a thread block --
+// two records per thread -- are counting-sorted by K through shared memory and dealt out in two passes:
+// thread i takes the i-th longest job, then the i-th shortest.  The lanes of a warp then run about the same
+// number of rows in each pass, and every warp of the block about the same number in total.
+constexpr int LZ_SPEC_JOBS = 2 * LZ_SPEC_THREADS;
 template <class PT>
 __global__ void __launch_bounds__(LZ_SPEC_THREADS)
 k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
@@ -371,24 +373,29 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
 {
     struct Item { const Rec* q; const Rec* r; int si0, sP0, K; uint32_t succ; };
     __shared__ uint32_t s_hist[64];
-    __shared__ uint16_t s_order[LZ_SPEC_THREADS];
-    __shared__ Item s_item[LZ_SPEC_THREADS];
+    __shared__ uint16_t s_order[LZ_SPEC_JOBS];
+    __shared__ Item s_item[LZ_SPEC_JOBS];
     const uint32_t total = *rec_total;
     const uint32_t tid = threadIdx.x;
-    const uint32_t t = blockIdx.x * (uint32_t)LZ_SPEC_THREADS + tid;
+    const uint32_t base = blockIdx.x * (uint32_t)LZ_SPEC_JOBS;
     if (tid < 64) s_hist[tid] = 0;
     __syncthreads();
-    SpecJob j; j.si0 = 0; j.sP0 = 0; j.K = -1; j.succ = 0; j.need = false;
-    if (t < total) {
-        const Rec rec = ld_rec(hit_recs + t);
-        const PairDesc d = desc[list[t].pair];
-        j = hit_spec_job(P, d.Dq - P.msl, list, (uint64_t)t, (uint64_t)total, rec);
-        if (j.need) s_item[tid] = Item{recs + d.q_rec, recs + d.r_rec, j.si0, j.sP0, j.K, j.succ};
-    }
-    uint32_t key = 63, rank = 0;
-    if (j.need) {
-        key = j.K < 0 ? 62u : (uint32_t)(SPEC_MAX_K - j.K);        // K <= SPEC_MAX_K = 57
-        rank = atomicAdd(&s_hist[key], 1u);
+    uint32_t key[2], rank[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t slot = tid + (uint32_t)h * LZ_SPEC_THREADS;
+        const uint32_t t = base + slot;
+        key[h] = 63; rank[h] = 0;
+        if (t < total) {
+            const Rec rec = ld_rec(hit_recs + t);
+            const PairDesc d = desc[list[t].pair];
+            const SpecJob j = hit_spec_job(P, d.Dq - P.msl, list, (uint64_t)t, (uint64_t)total, rec);
+            if (j.need) {
+                s_item[slot] = Item{recs + d.q_rec, recs + d.r_rec, j.si0, j.sP0, j.K, j.succ};
+                key[h] = j.K < 0 ? 62u : (uint32_t)(SPEC_MAX_K - j.K);        // K <= SPEC_MAX_K = 57: longest first
+                rank[h] = atomicAdd(&s_hist[key[h]], 1u);
+            }
+        }
     }
     __syncthreads();
     if (tid < 32) {                                                 // exclusive prefix over the 64 bins
@@ -403,16 +410,23 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
         s_hist[2 * tid + 1] = v - b;
     }
     __syncthreads();
-    if (j.need) s_order[s_hist[key] + rank] = (uint16_t)tid;
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+        if (key[h] != 63u) s_order[s_hist[key[h]] + rank[h]] = (uint16_t)(tid + (uint32_t)h * LZ_SPEC_THREADS);
     const uint32_t n_jobs = s_hist[63];                             // bin 63 is never used: its prefix is the job count
     __syncthreads();
-    if (tid < n_jobs) {
-        const uint32_t o = s_order[tid];
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        // pass 0: the tid-th longest job; pass 1: the tid-th shortest of those left
+        uint32_t jx;
+        if (pass == 0) { if (tid >= n_jobs) continue; jx = tid; }
+        else { if (n_jobs <= (uint32_t)LZ_SPEC_THREADS || tid >= n_jobs - (uint32_t)LZ_SPEC_THREADS) continue; jx = n_jobs - 1u - tid; }
+        const uint32_t o = s_order[jx];
         const Item it = s_item[o];
         PairView pv{};
         pv.q = it.q; pv.r = it.r;
         const int ks = spec_first_seed(pv, P, it.si0, it.sP0, it.K);
-        const uint32_t to = blockIdx.x * (uint32_t)LZ_SPEC_THREADS + o;
+        const uint32_t to = base + o;
         Rec r2 = ld_rec(hit_recs + to);
         SpecJob jj; jj.si0 = it.si0; jj.sP0 = it.sP0; jj.K = it.K; jj.succ = it.succ; jj.need = true;
         hit_spec_finish(r2, jj, ks);
@@ -686,7 +700,7 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
             cudaError_t e1 = cudaGetLastError();
             if (e1 != cudaSuccess) return e1;
             if (decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K)
-                k_hit_spec<<<(unsigned)((n_recs + LZ_SPEC_THREADS - 1) / LZ_SPEC_THREADS), LZ_SPEC_THREADS, 0, st>>>(
+                k_hit_spec<<<(unsigned)((n_recs + LZ_SPEC_JOBS - 1) / LZ_SPEC_JOBS), LZ_SPEC_THREADS, 0, st>>>(
                     recs, B.desc, B.list, B.rec_off + n_words, PT, B.recs);
             return cudaGetLastError();
         });
