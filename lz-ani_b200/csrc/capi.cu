@@ -695,7 +695,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     }
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
                                                   c->d_bitmap, c->d_table, c->d_out));
-                    T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 3 : 2) : 0);
+                    T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 1) : 0);
                     ++c->staged_chunks;
                 }
                 for (auto& sl : c->slot) {

@@ -139,7 +139,7 @@ k_parse_pairs(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta,
 //   S2 k_expand_hits   thread per word        hit list: (pair, position, run length) per hit run
 //   S3 k_hit_probe     thread per hit run     table probe, match length, both approximate extensions
 //      k_hit_spec      thread per hit run     speculative seed scan (jobs sorted by length per block)
-//      k_link_records  thread per hit run     successor links -> one 16-byte record per hit run
+//                                             + successor link -> one 16-byte record per hit run
 //   S4 k_walk_pairs    warp per pair          the state machine of parser.cpp:501-708 over the records
 template <class PT>
 __global__ void __launch_bounds__(256)
@@ -430,24 +430,13 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
         Rec r2 = ld_rec(hit_recs + to);
         SpecJob jj; jj.si0 = it.si0; jj.sP0 = it.sP0; jj.K = it.K; jj.succ = it.succ; jj.need = true;
         hit_spec_finish(r2, jj, ks);
+        // successor link (verified_link): needs this record complete and, of the successor, only what
+        // k_hit_probe wrote (position, anchor, flags, backward extension) -- bits no k_hit_spec thread changes,
+        // so it does not matter whether the successor's own scan has been folded in yet
+        const uint32_t d = r2.x >> HIT_ENTRY_RUN_SHIFT;
+        if (d && verified_link(P, r2, ld_rec(hit_recs + to + d)) != d) r2.x &= (uint32_t)(LZ_STAGED_MAX_POS - 1);
         reinterpret_cast<uint4*>(hit_recs)[to] = make_uint4(r2.x, r2.y, r2.z, r2.w);
     }
-}
-
-// S3c.  Successor links: record t keeps the offset of its successor only if the walk's next step after t
-// is a plain fast-path event on that successor (verified_link).  Reads the records as k_hit_records left
-// them; only bits [29,32) of x change (the position bits other threads read stay as they are).
-template <class PT>
-__global__ void __launch_bounds__(256)
-k_link_records(Rec* __restrict__ hit_recs, const uint32_t* __restrict__ rec_total, PT P)
-{
-    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
-    if (t >= *rec_total) return;
-    const Rec a = ld_rec(hit_recs + t);
-    const uint32_t d = a.x >> HIT_ENTRY_RUN_SHIFT;
-    if (!d) return;
-    const uint32_t keep = verified_link(P, a, ld_rec(hit_recs + t + d));
-    if (keep != d) hit_recs[t].x = a.x & (uint32_t)(LZ_STAGED_MAX_POS - 1);
 }
 
 template <class PT>
@@ -702,13 +691,6 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
             if (decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K)
                 k_hit_spec<<<(unsigned)((n_recs + LZ_SPEC_JOBS - 1) / LZ_SPEC_JOBS), LZ_SPEC_THREADS, 0, st>>>(
                     recs, B.desc, B.list, B.rec_off + n_words, PT, B.recs);
-            return cudaGetLastError();
-        });
-        if (e != cudaSuccess) return e;
-    }
-    if (n_recs) {
-        cudaError_t e = with_prm(P, [&](auto PT) {
-            k_link_records<<<(unsigned)((n_recs + 255) / 256), 256, 0, st>>>(B.recs, B.rec_off + n_words, PT);
             return cudaGetLastError();
         });
         if (e != cudaSuccess) return e;

@@ -1275,7 +1275,7 @@ LZ_HD void hit_spec_finish(Rec& rec, const SpecJob& j, int ks)
     rec.x |= j.succ << HIT_ENTRY_RUN_SHIFT;
 }
 
-// ---- successor links (k_link_records, one thread per record).  hit_record() left in x[29,32) the offset of
+// ---- successor links (decided at the end of k_hit_spec, one thread per record).  hit_record() left in x[29,32) the offset of
 // the first record at or after the window its record opens (0: none).  If the walk takes record `a` entirely
 // from its fields (the fast path of parse_pair), what happens next depends on nothing but a and that
 // successor b: this decides whether it is again one of the two plain fast-path events -- b inside the window,

@@ -82,15 +82,20 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
     }
     std::vector<Rec> recs(list.size() + 1);
     for (size_t t = 0; t < list.size(); ++t) recs[t] = hit_record_probe(pv, P, list.data(), t, true, [] {});      // k_hit_probe
-    for (size_t t = 0; t < list.size(); ++t) {                                                                    // k_hit_spec
+    // k_hit_spec: scan, then the successor link.  The kernel's threads run in any order: the link must come out
+    // the same whether the successor's own scan has been folded in yet (here: ascending = never; checked below
+    // against descending = always)
+    std::vector<uint32_t> link(list.size(), 0u);
+    for (size_t t = 0; t < list.size(); ++t) {
         const SpecJob j = hit_spec_job(P, n_loop, list.data(), t, list.size(), recs[t]);
         if (j.need) hit_spec_finish(recs[t], j, spec_first_seed(pv, P, j.si0, j.sP0, j.K));
+        const uint32_t d = recs[t].x >> HIT_ENTRY_RUN_SHIFT;
+        link[t] = d ? verified_link(P, recs[t], recs[t + d]) : 0u;          // successor as k_hit_probe left it
     }
-    // k_link_records: the link of every record is decided from the records as hit_record() left them
-    std::vector<uint32_t> link(list.size());
     for (size_t t = 0; t < list.size(); ++t) {
         const uint32_t d = recs[t].x >> HIT_ENTRY_RUN_SHIFT;
-        link[t] = d ? verified_link(P, recs[t], recs[t + d]) : 0u;
+        const uint32_t after = d ? verified_link(P, recs[t], recs[t + d]) : 0u;   // successor with its scan (and tentative link)
+        if (after != link[t]) ++lz_spec_mismatches;
     }
     for (size_t t = 0; t < list.size(); ++t)
         recs[t].x = (recs[t].x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) | (link[t] << HIT_ENTRY_RUN_SHIFT);
