@@ -7,7 +7,7 @@ Workload (BASELINE.json configs[1]): seeded synthetic viral genomes, ~50 kb, fam
 with 1-30 % divergence + indels + block events (lz-ani_b200/synth.py, seed 20261104), all2all,
 default parameters.  One STEP = one pass of the hot path over the whole pair list of this rank:
 reference index build (K2) + the staged parse (K3: per chunk of pairs the data-parallel scan / expand /
-probe / spec / link kernels and the warp-per-pair walk; LZANI_STAGED=0 selects the one-kernel form).  N=1: G = 2000 genomes -> 3 998 000
+probe / spec kernels and the warp-per-pair walk; LZANI_STAGED=0 selects the one-kernel form).  N=1: G = 2000 genomes -> 3 998 000
 ordered pairs per step.  N>1 (one process per GPU, torchrun): WEAK scaling -- the set grows to
 G_N = round(G*sqrt(N)) genomes so that every rank keeps ~G*(G-1) pairs; rank r owns reference
 rows r, r+N, ... (pair list sharded by reference block, sequences replicated, no collective
@@ -284,7 +284,7 @@ def main():
         assert out.astype(np.int64).sum(axis=0).tolist() == checksum, "e2e results differ from the resident run"
 
     # ---- roofline of the parse stage, per step.  The parse is a pipeline of kernels per chunk of pairs
-    # (scan, expand, probe, spec, link, walk; k_walk_pairs is the dominant one, see profiles/*_launch_summary.txt);
+    # (scan, expand, probe, spec, walk; k_walk_pairs is the dominant one, see profiles/*_launch_summary.txt);
     # SURVEY 8d's algorithmic bytes (4.375 B per query base + 12 B per pair) are those of the WHOLE parse of a
     # pair, so they are divided by the time of the whole stage (CUDA events around it on the library's
     # stream), not by the walk kernel's share of it.
@@ -292,7 +292,7 @@ def main():
     alg_bytes = BYTES_PER_QUERY_BASE * my_qbases + 12.0 * my_pairs
     achieved = alg_bytes / (parse_ms / args.steps / 1e3) / 1e9 if parse_ms > 0 else 0.0
     staged = os.environ.get("LZANI_STAGED", "1") != "0"
-    roofline = {"bound": "hbm", "kernel": "parse stage: k_scan_matrix + k_expand_hits + k_hit_probe + k_hit_spec + k_link_records + k_walk_pairs (dominant)" if staged else "k_parse_pairs",
+    roofline = {"bound": "hbm", "kernel": "parse stage: k_scan_matrix + k_expand_hits + k_hit_probe + k_hit_spec + k_walk_pairs (dominant)" if staged else "k_parse_pairs",
                 "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": measured_traffic(n, world) if staged else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": parse_ms / args.steps,
