@@ -666,7 +666,8 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         const uint32_t ja = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k0) - row_off.begin()) - 1;
                         const uint32_t jb = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k1 - 1) - row_off.begin());
                         if (row_off[ja] == ch.k0 && row_off[jb] == ch.k1) {
-                            if (!sl.mc) LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) << (2 * P.mal)));
+                            // 4^mal words, written 32 at a time (k_bitmap_matrix): never fewer than 32
+                            if (!sl.mc) LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) * std::max<uint64_t>(32, (uint64_t)1 << (2 * P.mal))));
                             mx.mc = sl.mc; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
                             use_mx = true;
                         }

@@ -1121,6 +1121,7 @@ LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int e
             const uint32_t km = low_mask32(P.mal);
             const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
             const uint32_t omask = (cmask >> 5) << 2;
+            const uint32_t bmask = cmask < 31u ? cmask : 31u;       // bitmaps below 32 bits (mal <= 2): the bit index needs masking too
 #if defined(__CUDA_ARCH__)
 #pragma unroll 8
 #endif
@@ -1128,7 +1129,7 @@ LZ_HD uint32_t scan_word_coarse(const PairView& pv, const PT& P, int pos0, int e
                 const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
                 const uint32_t sel = (lo & km) | (hs & ~km);
                 const uint32_t cwd = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(coarse) + ((sel >> 3) & omask));
-                m = funnel_r(m, funnel_r(cwd, 0u, (int)(sel & 31u)), 1);
+                m = funnel_r(m, funnel_r(cwd, 0u, (int)(sel & bmask)), 1);
             }
         } else {
 #if defined(__CUDA_ARCH__)

@@ -40,6 +40,8 @@ def test_kernel_source_matches_reference_golden(emul, case):
     (22, dict(mal=17, msl=10, mrd=33, mqd=90, reg=50, aw=32, am=12, ar=5)),   # hashed bitmap, 64-bit keys
     (23, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1)),         # tiny everything
     (24, dict(mal=11, msl=11, mrd=100, mqd=200, reg=35, aw=15, am=15, ar=3)), # am >= aw: never breaks
+    (25, dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1)),          # 16-bit bitmap: every position hits
+    (26, dict(mal=1, msl=1, mrd=2, mqd=1, reg=2, aw=2, am=0, ar=1)),          # 4-bit bitmap
 ])
 def test_kernel_source_vs_oracle_on_fresh_inputs(emul, seed, params):
     names, seqs = synth.families(2, 4, 1500, 4000, seed=seed, block=(100, 400))
@@ -111,7 +113,8 @@ def test_transpose32_is_a_bit_matrix_transpose(emul):
         assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize("params", [None, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1)])
+@pytest.mark.parametrize("params", [None, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1),
+                                    dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1)])
 def test_matrix_scan_equals_probe_scan(emul, params):
     """all2all form of the scan (bitmaps of 32 references transposed into one word per k-mer, one gather per
     query position, transpose back) against scan_word(), incl. N runs and the end of the loop."""
