@@ -42,6 +42,10 @@ def test_kernel_source_matches_reference_golden(emul, case):
     (24, dict(mal=11, msl=11, mrd=100, mqd=200, reg=35, aw=15, am=15, ar=3)), # am >= aw: never breaks
     (25, dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1)),          # 16-bit bitmap: every position hits
     (26, dict(mal=1, msl=1, mrd=2, mqd=1, reg=2, aw=2, am=0, ar=1)),          # 4-bit bitmap
+    (27, dict(mal=12, msl=7, mrd=40, mqd=40, reg=35, aw=15, am=7, ar=3)),     # direct 24-bit bitmap: folded scan + exact check
+    (28, dict(mal=11, msl=7, mrd=60, mqd=90, reg=35, aw=15, am=7, ar=3)),     # default k-mers, window too long for seed records
+    (29, dict(mal=11, msl=7, mrd=10, mqd=57, reg=20, aw=15, am=7, ar=3)),     # seed records at their longest scan, two-word rows
+    (30, dict(mal=11, msl=7, mrd=70, mqd=20, reg=35, aw=15, am=7, ar=3)),     # three-word rows from the start
 ])
 def test_kernel_source_vs_oracle_on_fresh_inputs(emul, seed, params):
     names, seqs = synth.families(2, 4, 1500, 4000, seed=seed, block=(100, 400))

@@ -40,6 +40,10 @@ def test_cuda_matches_reference_golden(case):
     (33, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1)),
     (35, dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1)),          # 16-bit bitmap: every position hits, record buffers overflow
     (36, dict(mal=1, msl=1, mrd=2, mqd=1, reg=2, aw=2, am=0, ar=1)),          # 4-bit bitmap
+    (37, dict(mal=12, msl=7, mrd=40, mqd=40, reg=35, aw=15, am=7, ar=3)),     # direct 24-bit bitmap: probe scan, fold + exact check
+    (38, dict(mal=11, msl=7, mrd=60, mqd=90, reg=35, aw=15, am=7, ar=3)),     # default k-mers, window too long for seed records
+    (39, dict(mal=11, msl=7, mrd=10, mqd=57, reg=20, aw=15, am=7, ar=3)),     # seed records at their longest scan
+    (40, dict(mal=11, msl=7, mrd=70, mqd=20, reg=35, aw=15, am=7, ar=3)),     # three-word rows from the start
     (34, dict(mal=11, msl=11, mrd=100, mqd=200, reg=35, aw=15, am=15, ar=3)),
     (35, dict(mal=15, msl=9, mrd=80, mqd=80, reg=100, aw=20, am=9, ar=4)),
 ])
