@@ -36,7 +36,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
     srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "pairlist.cu", "capi.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "regions.h", "simt.h", "outfilter.h")] + [
+    deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "lane_walk.h", "regions.h", "simt.h", "outfilter.h")] + [
         os.path.join(ROOT, "include", "lzani_b200.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH

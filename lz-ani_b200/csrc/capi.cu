@@ -81,6 +81,8 @@ struct lzani_ctx {
     uint64_t staged_words = 0;            // words per chunk (LZANI_STAGED_WORDS; 0: sized from the free HBM at the first run)
     uint64_t staged_recs = 0;             // record capacity per chunk (LZANI_STAGED_RECS; 0: 1.25 per word)
     int walk_blocks_per_sm = 1;
+    int lane_walk = 1;                    // 0: warp-per-pair walk k_walk_pairs (LZANI_LANE_WALK=0)
+    int lane_blocks_per_sm = 1;
     double rec_per_word = 1.0;            // observed hit runs per 32 query positions (chunk sizing)
     uint32_t staged_chunks = 0;           // of the last run
 
@@ -129,7 +131,8 @@ void free_sequences(lzani_ctx* c)
 void free_slot(lzani_ctx::Slot& s)
 {
     cudaFree(s.B.desc); cudaFree(s.B.n_words); cudaFree(s.B.word_off); cudaFree(s.B.hm); cudaFree(s.B.rec_off);
-    cudaFree(s.B.list); cudaFree(s.B.recs); cudaFree(s.B.tmp); cudaFree(s.B.wpair);
+    cudaFree(s.B.list); cudaFree(s.B.recs); cudaFree(s.B.tmp); cudaFree(s.B.wpair); cudaFree(s.B.hard);
+    s.B.hard = nullptr;
     s.B.desc = nullptr; s.B.n_words = nullptr; s.B.word_off = nullptr; s.B.hm = nullptr; s.B.rec_off = nullptr; s.B.wpair = nullptr;
     s.B.list = nullptr; s.B.recs = nullptr; s.B.tmp = nullptr; s.B.tmp_bytes = 0;
     s.pairs_cap = s.words_cap = s.recs_cap = 0;
@@ -139,9 +142,10 @@ void free_slot(lzani_ctx::Slot& s)
 int ensure_slot(lzani_ctx* c, lzani_ctx::Slot& s, uint64_t pairs, uint64_t words, uint64_t recs)
 {
     if (pairs > s.pairs_cap) {
-        cudaFree(s.B.desc); cudaFree(s.B.n_words); cudaFree(s.B.word_off);
-        s.B.desc = nullptr; s.B.n_words = nullptr; s.B.word_off = nullptr; s.pairs_cap = 0;
+        cudaFree(s.B.desc); cudaFree(s.B.n_words); cudaFree(s.B.word_off); cudaFree(s.B.hard);
+        s.B.desc = nullptr; s.B.n_words = nullptr; s.B.word_off = nullptr; s.B.hard = nullptr; s.pairs_cap = 0;
         LZ_CUDA(c, cudaMalloc((void**)&s.B.desc, sizeof(PairDesc) * pairs));
+        LZ_CUDA(c, cudaMalloc((void**)&s.B.hard, sizeof(uint32_t) * pairs));
         LZ_CUDA(c, cudaMalloc((void**)&s.B.n_words, sizeof(uint32_t) * (pairs + 1)));
         LZ_CUDA(c, cudaMalloc((void**)&s.B.word_off, sizeof(uint32_t) * (pairs + 1)));
         s.pairs_cap = pairs;
@@ -222,6 +226,9 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     LZ_CUDA(c, cudaMalloc((void**)&c->d_reg_counter, sizeof(unsigned long long)));
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
     c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
+    c->lane_blocks_per_sm = lane_blocks_per_sm(c->P);
+    if (const char* e = getenv("LZANI_LANE_WALK")) c->lane_walk = atoi(e);
+    if (const char* e = getenv("LZANI_LANE_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->lane_blocks_per_sm) c->lane_blocks_per_sm = v; }
     if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
     if (const char* e = getenv("LZANI_STAGED_RECS")) { const long long v = atoll(e); if (v > 0) c->staged_recs = (uint64_t)v; }
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
@@ -232,7 +239,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
         LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
         LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, sizeof(uint32_t)));
-        LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, sizeof(unsigned long long)));
+        LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, 4 * sizeof(unsigned long long)));
     }
     return LZANI_OK;
 }
@@ -695,8 +702,10 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         if (int rc = ensure_slot(c, sl, sl.pairs_cap, sl.words_cap, n_hit)) return rc;
                     }
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
-                                                  c->d_bitmap, c->d_table, c->d_out));
-                    T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 1) : 0);
+                                                  c->d_bitmap, c->d_table, c->d_out,
+                                                  c->lane_walk ? c->n_sm * c->lane_blocks_per_sm : 0));
+                    T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 1) : 0) +
+                                  (c->lane_walk && is_default_kernel_params(P) && P.mqd <= 57 ? 1 : 0);
                     ++c->staged_chunks;
                 }
                 for (auto& sl : c->slot) {

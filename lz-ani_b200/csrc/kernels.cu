@@ -14,6 +14,7 @@
 
 #include "kernels.h"
 #include "parse_core.h"
+#include "lane_walk.h"
 
 namespace lzani {
 
@@ -425,7 +426,7 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
         const Item it = s_item[o];
         PairView pv{};
         pv.q = it.q; pv.r = it.r;
-        const int ks = spec_first_seed(pv, P, it.si0, it.sP0, it.K);
+        const int ks = spec_first_seed(pv, P, it.si0, it.sP0, it.K, P.mrd);
         const uint32_t to = base + o;
         Rec r2 = ld_rec(hit_recs + to);
         SpecJob jj; jj.si0 = it.si0; jj.sP0 = it.sP0; jj.K = it.K; jj.succ = it.succ; jj.need = true;
@@ -445,19 +446,102 @@ k_walk_pairs(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
              const uint32_t* __restrict__ rec_off, const Rec* __restrict__ hit_recs, uint32_t n_pairs,
              uint64_t pair_begin, PT P, const uint32_t* __restrict__ bitmap_pool,
              const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
-             int3* __restrict__ out)
+             int3* __restrict__ out, const uint32_t* __restrict__ list, const unsigned long long* __restrict__ n_list)
 {
+    // list != nullptr: only the pairs list[0 .. *n_list) -- the ones k_walk_lanes handed over
     DevWarp w((int)(threadIdx.x & 31u));
+    const unsigned long long n_todo = list ? *n_list : (unsigned long long)n_pairs;
     for (;;) {
         unsigned long long k = 0;
         if (w.lane == 0) k = atomicAdd(counter, 1ull);
         k = __shfl_sync(0xFFFFFFFFu, k, 0);
-        if (k >= n_pairs) return;
-        const uint32_t pl = (uint32_t)k;
+        if (k >= n_todo) return;
+        const uint32_t pl = list ? list[k] : (uint32_t)k;
         const PairView pv = view_of(desc[pl], recs, bitmap_pool, table_pool);
         const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
         const PairResult res = walk_pair(w, pv, P, hit_recs + r0, r1 - r0);
         if (w.lane == 0) out[pair_begin + pl] = make_int3(res.m, res.x, res.n);
+    }
+}
+
+// S4, lane form (lane_walk.h): every LANE walks its own pair.  A lane takes the plain events of its pair straight
+// from the records (lane_run_step); when it meets anything else it parks -- for the general step (lane_slow_step:
+// seed and close matches, deferred anchors, long extensions, the tail) or for the seed scan of a window no
+// record describes (lane_scan_step) -- and the warp enters a parked step only once LZ_LANE_PARK_SLOW /
+// LZ_LANE_PARK_SCAN lanes wait for it (or nobody can run, or they have waited LZ_LANE_WAIT rounds), so the
+// expensive code runs with many active lanes.  Lanes pull new pairs as they finish (consecutive pairs of a
+// chunk share their reference).
+template <class PT>
+__device__ LZ_LANE_SLOW_ATTR LaneCtx lane_slow_call(LaneCtx L, PT P)
+{
+    lane_slow_step(L, P);
+    return L;
+}
+template <class PT>
+__device__ LZ_LANE_SLOW_ATTR LaneCtx lane_scan_call(LaneCtx L, PT P)
+{
+    lane_scan_step(L, P);
+    return L;
+}
+
+template <class PT>
+__global__ void __launch_bounds__(LZ_LANE_THREADS, LZ_LANE_MIN_BLOCKS)
+k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off,
+             const uint32_t* __restrict__ rec_off, const Rec* __restrict__ hit_recs, uint32_t n_pairs,
+             uint64_t pair_begin, PT P, const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
+             int3* __restrict__ out, uint32_t* __restrict__ hard_list, unsigned long long* __restrict__ hard_count)
+{
+    LaneCtx L;
+    L.mode = LANE_DONE;
+    uint32_t pl = 0xFFFFFFFFu;
+    bool more = true;
+    int w_slow = 0, w_scan = 0;           // rounds the parked lanes have waited
+    int parks = 0, park_limit = 0;        // parked steps of this lane's pair; beyond the limit the pair is handed over
+    for (;;) {
+        if (L.mode == LANE_DONE) {
+            if (pl != 0xFFFFFFFFu) {
+                out[pair_begin + pl] = make_int3(L.s.totM, L.s.totX, L.s.totN);
+                pl = 0xFFFFFFFFu;
+            }
+            if (more) {
+                const unsigned long long k = atomicAdd(counter, 1ull);
+                if (k < n_pairs) {
+                    pl = (uint32_t)k;
+                    const PairView pv = view_of(desc[pl], recs, nullptr, table_pool);
+                    const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
+                    lane_begin(L, pv, hit_recs + r0, r1 - r0, P.msl);
+                    parks = 0;
+                    park_limit = LZ_LANE_HARD_BASE + (L.n_loop >> LZ_LANE_HARD_SHIFT);
+                } else more = false;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, L.mode != LANE_DONE)) return;
+#pragma unroll 1
+        for (int r = 0; r < LZ_LANE_RUN_STEPS; ++r)
+            if (L.mode == LANE_RUN) lane_run_step(L, P);
+        __syncwarp();
+        bool any_run = __any_sync(0xFFFFFFFFu, L.mode == LANE_RUN);
+        const int n_slow = __popc(__ballot_sync(0xFFFFFFFFu, L.mode == LANE_SLOW));
+        if (n_slow && (n_slow >= LZ_LANE_PARK_SLOW || !any_run || ++w_slow >= LZ_LANE_WAIT)) {
+            if (L.mode == LANE_SLOW) {
+                if (++parks > park_limit && L.s.i < L.n_loop) {
+                    // a pair that lives in the general code (related genomes: hundreds of seed / close matches): the
+                    // warp-per-pair walk does those steps 32 lanes wide -- hand the pair over (k_walk_pairs restarts it)
+                    hard_list[atomicAdd(hard_count, 1ull)] = pl;
+                    pl = 0xFFFFFFFFu;
+                    L.mode = LANE_DONE;
+                } else L = lane_slow_call(L, P);
+            }
+            __syncwarp();
+            w_slow = 0;
+            any_run = __any_sync(0xFFFFFFFFu, L.mode == LANE_RUN);
+        }
+        const int n_scan = __popc(__ballot_sync(0xFFFFFFFFu, L.mode == LANE_SCAN));
+        if (n_scan && (n_scan >= LZ_LANE_PARK_SCAN || !any_run || ++w_scan >= LZ_LANE_WAIT)) {
+            if (L.mode == LANE_SCAN) { ++parks; L = lane_scan_call(L, P); }
+            __syncwarp();
+            w_scan = 0;
+        }
     }
 }
 
@@ -615,6 +699,16 @@ int walk_blocks_per_sm(const Prm& P)
     return nb;
 }
 
+int lane_blocks_per_sm(const Prm& P)
+{
+    int nb = 0;
+    const cudaError_t e = is_default_kernel_params(P)
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_lanes<PrmDefault>, LZ_LANE_THREADS, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_lanes<Prm>, LZ_LANE_THREADS, 0);
+    if (e != cudaSuccess || nb < 1) nb = 1;
+    return nb;
+}
+
 size_t staged_scan_bytes(uint64_t n_items)
 {
     size_t a = 0, b = 0;
@@ -675,7 +769,7 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
 
 cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
                                uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,
-                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out)
+                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out, int lane_grid_blocks)
 {
     if (n_words) {
         k_expand_hits<<<(unsigned)((n_words + 255) / 256), 256, 0, st>>>(B.hm, B.wpair, B.word_off, (uint32_t)n_words, B.rec_off, B.list);
@@ -695,11 +789,24 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
         });
         if (e != cudaSuccess) return e;
     }
-    cudaError_t e = cudaMemsetAsync(B.counter, 0, sizeof(unsigned long long), st);
+    // counter[0]: pairs pulled by the first walk kernel, [1]: by the second, [2]: pairs handed over
+    cudaError_t e = cudaMemsetAsync(B.counter, 0, 3 * sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     return with_prm(P, [&](auto PT) {
-        k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
-                                                            PT, bitmap_pool, table_pool, B.counter, reinterpret_cast<int3*>(out));
+        if (lane_grid_blocks > 0 && decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K) {
+            // lane per pair; the few pairs that live in the general code are handed to the warp-per-pair walk
+            k_walk_lanes<<<lane_grid_blocks, LZ_LANE_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
+                                                                     PT, table_pool, B.counter, reinterpret_cast<int3*>(out), B.hard,
+                                                                     B.counter + 2);
+            const cudaError_t e1 = cudaGetLastError();
+            if (e1 != cudaSuccess) return e1;
+            k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
+                                                                PT, bitmap_pool, table_pool, B.counter + 1, reinterpret_cast<int3*>(out),
+                                                                B.hard, B.counter + 2);
+        } else
+            k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
+                                                                PT, bitmap_pool, table_pool, B.counter, reinterpret_cast<int3*>(out),
+                                                                nullptr, nullptr);
         return cudaGetLastError();
     });
 }

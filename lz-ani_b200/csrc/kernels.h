@@ -20,6 +20,37 @@
 #ifndef LZ_WALK_MIN_BLOCKS
 #define LZ_WALK_MIN_BLOCKS 5
 #endif
+// lane-per-pair walk (k_walk_lanes): block size, resident blocks, plain events per round, parked lanes that
+// trigger the general step / the seed scan, rounds a parked lane waits at most
+#ifndef LZ_LANE_THREADS
+#define LZ_LANE_THREADS 128
+#endif
+#ifndef LZ_LANE_MIN_BLOCKS
+#define LZ_LANE_MIN_BLOCKS 4
+#endif
+#ifndef LZ_LANE_RUN_STEPS
+#define LZ_LANE_RUN_STEPS 4
+#endif
+#ifndef LZ_LANE_PARK_SLOW
+#define LZ_LANE_PARK_SLOW 12
+#endif
+#ifndef LZ_LANE_PARK_SCAN
+#define LZ_LANE_PARK_SCAN 16
+#endif
+#ifndef LZ_LANE_WAIT
+#define LZ_LANE_WAIT 8
+#endif
+// a lane hands its pair to the warp-per-pair walk after BASE + (query positions >> SHIFT) parked steps (an unrelated
+// 50 kb pair parks ~120 times, a related one 600-1300 times)
+#ifndef LZ_LANE_HARD_BASE
+#define LZ_LANE_HARD_BASE 64
+#endif
+#ifndef LZ_LANE_HARD_SHIFT
+#define LZ_LANE_HARD_SHIFT 8
+#endif
+#ifndef LZ_LANE_SLOW_ATTR
+#define LZ_LANE_SLOW_ATTR __forceinline__
+#endif
 #ifndef LZ_RECORD_THREADS
 #define LZ_RECORD_THREADS 256
 #endif
@@ -71,7 +102,8 @@ struct StagedBufs {
     HitEntry* list;               // [records]
     Rec* recs;                    // [records]
     void* tmp; size_t tmp_bytes;  // CUB scan scratch
-    unsigned long long* counter;
+    unsigned long long* counter;  // [3] work counters of the walk kernels
+    uint32_t* hard;               // [pairs] pairs the lane walk hands to the warp walk
 };
 // all2all form of the scan (k_bitmap_matrix + k_scan_matrix): the chunk is made of whole dense rows
 struct MatrixScan {
@@ -82,6 +114,7 @@ struct MatrixScan {
     uint32_t max_words;           // longest query, in 32-position words
 };
 int walk_blocks_per_sm(const Prm& P);
+int lane_blocks_per_sm(const Prm& P);
 size_t staged_scan_bytes(uint64_t n_items);
 // S0, scan, S1, scan: afterwards rec_off[n_words] holds the number of records of the chunk
 cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
@@ -92,7 +125,8 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
 // S2, S3, S4
 cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
                                uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,
-                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out);
+                               const uint32_t* bitmap_pool, const uint64_t* table_pool, void* out,
+                               int lane_grid_blocks = 0);       // > 0: the lane-per-pair walk (k_walk_lanes) on that many blocks
 
 // ---- postproc.cu: pairing of the two directions, derived metrics, --out-filter compaction
 // where the results of reference row r live (this GPU or a peer): res[i] is the result of the i-th

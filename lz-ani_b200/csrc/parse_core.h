@@ -675,9 +675,9 @@ static long lz_spec_used = 0, lz_spec_mismatches = 0, lz_pred_steps = 0, lz_batc
 #endif
 // four rows of the speculative seed scan (spec_first_seed below) on the first NW words of the window
 constexpr int SPEC_GO_ON = -2;
-template <int NW, class PT>
-LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, uint64_t ql, uint64_t qh, int mb, int K, V3& e_prev,
-                     V3 (&a2)[4], V3 (&a4)[4])
+template <int NW, bool kRefN, class PT>
+LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, const V3& rn, uint64_t ql, uint64_t qh, uint64_t qn, int mb, int K,
+                     int mrdx, V3& e_prev, V3 (&a2)[4], V3 (&a4)[4])
 {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -687,9 +687,16 @@ LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, uint64_t ql, uint6
         // all-ones where the query base's plane bit is 0: equal <=> (r ^ ~q) on both planes
         const uint32_t nl = ((uint32_t)(ql >> u) & 1u) - 1u, nh = ((uint32_t)(qh >> u) & 1u) - 1u;
         V3 eq;
-        eq.a = (rl.a ^ nl) & (rh.a ^ nh);
-        eq.b = (rl.b ^ nl) & (rh.b ^ nh);
-        eq.c = NW > 2 ? (rl.c ^ nl) & (rh.c ^ nh) : 0u;
+        if (kRefN) {       // an N equals nothing: reference N masked per word (still two LOP3), a query N empties its row
+            const uint32_t nq = ((uint32_t)(qn >> u) & 1u) - 1u;
+            eq.a = (rl.a ^ nl) & ((rh.a ^ nh) & ~rn.a) & nq;
+            eq.b = (rl.b ^ nl) & ((rh.b ^ nh) & ~rn.b) & nq;
+            eq.c = NW > 2 ? (rl.c ^ nl) & ((rh.c ^ nh) & ~rn.c) & nq : 0u;
+        } else {
+            eq.a = (rl.a ^ nl) & (rh.a ^ nh);
+            eq.b = (rl.b ^ nl) & (rh.b ^ nh);
+            eq.c = NW > 2 ? (rl.c ^ nl) & (rh.c ^ nh) : 0u;
+        }
         const V3 p2 = v3_and_shr<NW>(e_prev, eq, 1);                // A2_{m-1} = E_{m-1} & E_m>>1
         const V3 p4 = v3_and_shr<NW>(a2[(u + 1) % 4], p2, 2);       // A4_{m-3} = A2_{m-3} & A2_{m-1}>>2
         const V3 s7 = v3_and_shr<NW>(a4[(u + 2) % 4], p4, 3);       // S_{m-6}  = A4_{m-6} & A4_{m-3}>>3
@@ -698,7 +705,7 @@ LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, uint64_t ql, uint6
         e_prev = eq;
         if ((s7.a | s7.b | s7.c) && m >= 6) {
             const int k = m - 6;
-            const int nv = k + P.mrd;                               // valid reference offsets of row k: x < k + mrd
+            const int nv = k + mrdx;                                // valid reference offsets of row k: x < k + mrd (+ lit0)
             const uint32_t c0 = s7.a & low_mask32(nv > 32 ? 32 : nv);
             const uint32_t c1 = nv > 32 ? s7.b & low_mask32(nv - 32 > 32 ? 32 : nv - 32) : 0u;
             const uint32_t c2 = nv > 64 ? s7.c & low_mask32(nv - 64 > 32 ? 32 : nv - 64) : 0u;
@@ -713,23 +720,39 @@ LZ_HD int spec_rows4(const PT& P, const V3& rl, const V3& rh, uint64_t ql, uint6
     return SPEC_GO_ON;
 }
 
-template <class PT>
-LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K)
+// mrdx = mrd + (literals already behind the window's first position): P.mrd for the window a match opens
+// (k_hit_spec); the lane walk (lane_walk.h) also scans windows it has already walked lit0 positions into.
+// kRefN: N inside the reference window is handled (masked out of every row) instead of giving up -- the lane walk's
+// own scans; k_hit_spec uses the plain form (three registers fewer) and leaves such windows to the walk.
+template <bool kRefN, class PT>
+LZ_HD int spec_first_seed_t(const PairView& pv, const PT& P, int i0, int P0, int K, int mrdx)
 {
-    // window: query bases [i0, i0+K+7), reference bases [P0, P0+K+mrd+6)
-    if (K < 0 || K > SPEC_MAX_K || K + P.mrd + 6 > 96 || P0 < 0) return -1;
+    // window: query bases [i0, i0+K+7), reference bases [P0, P0+K+mrdx+6)
+    if (K < 0 || K > SPEC_MAX_K || K + mrdx + 6 > 96 || P0 < 0) return -1;
     const Planes64 Q = ext64(pv.q, i0);
-    const uint64_t qn = ((uint64_t)Q.nm1 << 32) | Q.nm0;
-    if (qn & low_mask64(K + 7)) return -1;
-    V3 rl, rh;
+    uint64_t qn = (((uint64_t)Q.nm1 << 32) | Q.nm0) & low_mask64(K + 7);
+    if (qn) {
+        // an msl-mer over an N is no seed.  N from some base to the end of the window (every query ends like that):
+        // the rows from the first N - 6 on are empty -- scan the ones before.  N in the middle: masked row by row
+        // (kRefN) or left to the walk.
+        if ((qn | (qn - 1ull)) == low_mask64(K + 7)) {
+            K = ctz64(qn) - 7;
+            if (K < 0) return 64;
+            qn = 0;
+        } else if (!kRefN) return -1;
+    }
+    V3 rl, rh, rn{0, 0, 0};
     {
         const int wd = P0 >> 5, sh = P0 & 31;
         const Rec a = ld_rec(pv.r + wd), b = ld_rec(pv.r + wd + 1), c = ld_rec(pv.r + wd + 2), d = ld_rec(pv.r + wd + 3);
         rl.a = funnel_r(a.x, b.x, sh); rl.b = funnel_r(b.x, c.x, sh); rl.c = funnel_r(c.x, d.x, sh);
         rh.a = funnel_r(a.y, b.y, sh); rh.b = funnel_r(b.y, c.y, sh); rh.c = funnel_r(c.y, d.y, sh);
         const uint32_t n0 = funnel_r(a.z, b.z, sh), n1 = funnel_r(b.z, c.z, sh), n2 = funnel_r(c.z, d.z, sh);
-        const int nr = K + P.mrd + 6;      // <= 96
-        if (n0 | (nr > 32 ? (n1 & low_mask32(nr - 32 > 32 ? 32 : nr - 32)) : 0u) | (nr > 64 ? (n2 & low_mask32(nr - 64)) : 0u)) return -1;
+        const int nr = K + mrdx + 6;       // <= 96
+        if (kRefN) { rn.a = n0; rn.b = n1; rn.c = n2; }
+        else if ((nr >= 32 ? n0 : (n0 & low_mask32(nr))) | (nr > 32 ? (n1 & low_mask32(nr - 32 > 32 ? 32 : nr - 32)) : 0u) |
+                 (nr > 64 ? (n2 & low_mask32(nr - 64)) : 0u))
+            return -1;
     }
     uint64_t ql = ((uint64_t)Q.lo1 << 32) | Q.lo0, qh = ((uint64_t)Q.hi1 << 32) | Q.hi0;
     // MATCH masks E_m (bit x: r[P0+x] == q[i0+m]), AND-combined by doubling: pairs A2, fours A4, sevens S.
@@ -742,22 +765,30 @@ LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K
     V3 e_prev{0, 0, 0}, a2[4], a4[4];
     for (int u = 0; u < 4; ++u) a2[u] = a4[u] = V3{0, 0, 0};
     const int m_last = K + 6;
-    int m_two = 58 - P.mrd;                 // rows below this (rounded down to a group) need two words
+    int m_two = 58 - mrdx;                  // rows below this (rounded down to a group) need two words
     m_two = m_two > 0 ? m_two & ~3 : 0;
     int mb = 0;
     for (; mb < m_two && mb <= m_last; mb += 4) {
-        const int r = spec_rows4<2>(P, rl, rh, ql, qh, mb, K, e_prev, a2, a4);
+        const int r = spec_rows4<2, kRefN>(P, rl, rh, rn, ql, qh, qn, mb, K, mrdx, e_prev, a2, a4);
         if (r != SPEC_GO_ON) return r;
         ql >>= 4;
         qh >>= 4;
+        qn >>= 4;
     }
     for (; mb <= m_last; mb += 4) {
-        const int r = spec_rows4<3>(P, rl, rh, ql, qh, mb, K, e_prev, a2, a4);
+        const int r = spec_rows4<3, kRefN>(P, rl, rh, rn, ql, qh, qn, mb, K, mrdx, e_prev, a2, a4);
         if (r != SPEC_GO_ON) return r;
         ql >>= 4;
         qh >>= 4;
+        qn >>= 4;
     }
     return 64;
+}
+
+template <class PT>
+LZ_HD int spec_first_seed(const PairView& pv, const PT& P, int i0, int P0, int K, int mrdx)
+{
+    return spec_first_seed_t<false>(pv, P, i0, P0, K, mrdx);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1267,7 +1298,7 @@ LZ_HD SpecJob hit_spec_job(const PT& P, int n_loop, const HitEntry* list, uint64
     j.need = true;
     return j;
 }
-// ks = spec_first_seed(pv, P, j.si0, j.sP0, j.K)
+// ks = spec_first_seed(pv, P, j.si0, j.sP0, j.K, P.mrd)
 LZ_HD void hit_spec_finish(Rec& rec, const SpecJob& j, int ks)
 {
     if (ks < 0) return;              // no speculative seed record: the walk goes through the general code (no link)
@@ -1523,7 +1554,7 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                         while (idx < b_cnt && win_base + (int)(list[idx] & 0x1FFFu) < si0) ++idx;
                         int K = idx < b_cnt ? win_base + (int)(list[idx] & 0x1FFFu) - si0 : b_cover - 1 - si0;
                         if (K > P.mqd) K = P.mqd;
-                        const int ks = spec_first_seed(pv, P, si0, sP0, K);
+                        const int ks = spec_first_seed(pv, P, si0, sP0, K, P.mrd);
                         if (ks >= 0) {
                             r_w3[ln] |= ((uint32_t)(K + 1) << 18) | ((uint32_t)(ks & 127) << 24) | ((ks & SPEC_MULTI) ? 0x80000000u : 0u);
                             r_w2[ln] |= (uint32_t)((ks >> 8) & 127) << HIT_X_SHIFT;

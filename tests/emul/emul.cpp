@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../lz-ani_b200/csrc/parse_core.h"
+#include "../../lz-ani_b200/csrc/lane_walk.h"
 #include "../../lz-ani_b200/csrc/outfilter.h"
 
 using namespace lzani;
@@ -63,7 +64,7 @@ void build_index(HostIndex& ix, const HostSeq& s, const Prm& P)
 // the staged pipeline of kernels.cu for one pair: k_scan_hits / k_expand_hits / k_hit_records element by
 // element, then the walk over the stored records (k_walk_pairs)
 template <class PT>
-PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
+PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P, bool lane_walk)
 {
     const int n_loop = pv.Dq - P.msl;
     const int n_words = n_loop > 0 ? (n_loop + 31) / 32 : 0;
@@ -88,7 +89,7 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
     std::vector<uint32_t> link(list.size(), 0u);
     for (size_t t = 0; t < list.size(); ++t) {
         const SpecJob j = hit_spec_job(P, n_loop, list.data(), t, list.size(), recs[t]);
-        if (j.need) hit_spec_finish(recs[t], j, spec_first_seed(pv, P, j.si0, j.sP0, j.K));
+        if (j.need) hit_spec_finish(recs[t], j, spec_first_seed(pv, P, j.si0, j.sP0, j.K, P.mrd));
         const uint32_t d = recs[t].x >> HIT_ENTRY_RUN_SHIFT;
         link[t] = d ? verified_link(P, recs[t], recs[t + d]) : 0u;          // successor as k_hit_probe left it
     }
@@ -99,13 +100,15 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P)
     }
     for (size_t t = 0; t < list.size(); ++t)
         recs[t].x = (recs[t].x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) | (link[t] << HIT_ENTRY_RUN_SHIFT);
+    // k_walk_lanes (one lane per pair, lane_walk.h) or k_walk_pairs (one warp per pair)
+    if (lane_walk) return lane_walk_pair(pv, P, recs.data(), (uint32_t)list.size());
     return walk_pair(w, pv, P, recs.data(), (uint32_t)list.size());
 }
 
 }  // namespace
 
-static bool staged = false;
-extern "C" void lzani_emul_set_staged(int on) { staged = on != 0; }
+static int staged = 0;       // 0: one-kernel form, 1: staged + warp-per-pair walk, 2: staged + lane-per-pair walk
+extern "C" void lzani_emul_set_staged(int on) { staged = on; }
 
 extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const uint8_t* const* data,
                                       const uint32_t* len, uint32_t n_rows, const uint32_t* ref_ids,
@@ -143,8 +146,8 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 // same dispatch as launch_parse(): compile-time defaults or run-time parameters
                 PairResult res;
                 if (staged) {
-                    if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = staged_pair(w, pv, D); }
-                    else res = staged_pair(w, pv, P);
+                    if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = staged_pair(w, pv, D, staged == 2); }
+                    else res = staged_pair(w, pv, P, staged == 2);
                 } else if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch); }
                 else res = parse_pair(w, pv, P, &scratch);
                 out3[3 * k] = res.m; out3[3 * k + 1] = res.x; out3[3 * k + 2] = res.n;
@@ -169,6 +172,7 @@ extern "C" void lzani_emul_counters(long* c)
     c[16] = lz_chain;
     c[17] = lz_why[10];      // seed short cuts
 }
+extern "C" void lzani_emul_lane_why(long* c) { for (int i = 0; i < 16; ++i) c[i] = lz_lane_why[i]; }
 extern "C" void lzani_emul_spec_stats(long* used, long* mismatches)
 {
     *used = lz_spec_used;

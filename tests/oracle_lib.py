@@ -115,7 +115,8 @@ class Emul(_Checker):
         subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "tests", "emul")], check=True)
         super().__init__(EMUL_SO, "lzani_emul")
 
-    def set_staged(self, on: bool):
-        """False: the one-kernel form (the warp builds its batches itself); True: the staged pipeline
-        (hit records computed ahead per query position, the walk loads them)."""
-        self.lib.lzani_emul_set_staged(1 if on else 0)
+    def set_staged(self, on):
+        """0 / False: the one-kernel form (the warp builds its batches itself); 1 / True: the staged pipeline
+        (hit records computed ahead per query position) with the warp-per-pair walk; 2: the staged pipeline with
+        the lane-per-pair walk (lane_walk.h, the product's default)."""
+        self.lib.lzani_emul_set_staged(int(on))

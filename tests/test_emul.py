@@ -15,14 +15,17 @@ synth = importlib.import_module("lz-ani_b200.synth")
 GOLD = np.load(os.path.join(os.path.dirname(mg.__file__), "golden.npz"))
 
 
-@pytest.fixture(scope="module", params=["staged", "one_kernel"])
+FORMS = {"staged_lane": 2, "staged": 1, "one_kernel": 0}
+
+
+@pytest.fixture(scope="module", params=list(FORMS))
 def emul(request):
-    """Both forms of the parse: the staged pipeline (the product's default) and the one-kernel form
-    (regions kernel, LZANI_STAGED=0)."""
+    """All forms of the parse: the staged pipeline with the lane-per-pair walk (the product's default), with
+    the warp-per-pair walk (LZANI_LANE_WALK=0), and the one-kernel form (regions kernel, LZANI_STAGED=0)."""
     e = Emul()
-    e.set_staged(request.param == "staged")
+    e.set_staged(FORMS[request.param])
     yield e
-    e.set_staged(False)
+    e.set_staged(0)
 
 
 @pytest.mark.parametrize("case", list(mg.CASES))
@@ -70,6 +73,8 @@ def test_speculative_seed_records_agree_with_diagonal_scan(emul):
     emul.lib.lzani_emul_counters(c)
     if c[1] and c[16] + c[17]:          # staged form: links and seed short cuts were replayed against the serial rules
         assert c[16] > 1000 and c[17] > 50, (c[16], c[17])
+    if c[1] == 0 and c[5]:              # lane walk: plain events taken from records, row-wise seeds checked against diagonals
+        assert c[5] > 1000 and c[17] > 50, (c[5], c[17])
 
 
 @pytest.mark.parametrize("seed", list(range(100, 112)))
