@@ -226,9 +226,11 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     LZ_CUDA(c, cudaMalloc((void**)&c->d_reg_counter, sizeof(unsigned long long)));
     c->blocks_per_sm = parse_blocks_per_sm(c->P);
     c->walk_blocks_per_sm = walk_blocks_per_sm(c->P);
-    c->lane_blocks_per_sm = lane_blocks_per_sm(c->P);
+    // the lane walk is bound by dependent-instruction latency, not by occupancy: three resident blocks per SM do as well
+    // as five (measured, profiles/r02_walk_ab.txt) and leave registers for the other slot's data-parallel stages to run beside it
+    c->lane_blocks_per_sm = std::min(lane_blocks_per_sm(c->P), 3);
     if (const char* e = getenv("LZANI_LANE_WALK")) c->lane_walk = atoi(e);
-    if (const char* e = getenv("LZANI_LANE_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->lane_blocks_per_sm) c->lane_blocks_per_sm = v; }
+    if (const char* e = getenv("LZANI_LANE_BLOCKS")) { const int v = atoi(e); if (v > 0 && v <= lane_blocks_per_sm(c->P)) c->lane_blocks_per_sm = v; }
     if (const char* e = getenv("LZANI_STAGED")) c->staged = atoi(e);
     if (const char* e = getenv("LZANI_STAGED_RECS")) { const long long v = atoll(e); if (v > 0) c->staged_recs = (uint64_t)v; }
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);

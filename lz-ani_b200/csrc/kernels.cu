@@ -464,24 +464,46 @@ k_walk_pairs(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
     }
 }
 
-// S4, lane form (lane_walk.h): every LANE walks its own pair.  A lane takes the plain events of its pair straight
-// from the records (lane_run_step); when it meets anything else it parks -- for the general step (lane_slow_step:
-// seed and close matches, deferred anchors, long extensions, the tail) or for the seed scan of a window no
-// record describes (lane_scan_step) -- and the warp enters a parked step only once LZ_LANE_PARK_SLOW /
-// LZ_LANE_PARK_SCAN lanes wait for it (or nobody can run, or they have waited LZ_LANE_WAIT rounds), so the
-// expensive code runs with many active lanes.  Lanes pull new pairs as they finish (consecutive pairs of a
-// chunk share their reference).
-template <class PT>
-__device__ LZ_LANE_SLOW_ATTR LaneCtx lane_slow_call(LaneCtx L, PT P)
+// S4, lane form (lane_walk.h): every LANE walks its own pairs -- LZ_LANE_SLOTS of them at a time, their contexts
+// (21 words each) parked in shared memory.  Per round a lane takes up to LZ_LANE_RUN_STEPS plain events of one of
+// its runnable pairs straight from the records (lane_run_step).  A pair that meets anything else waits: for the
+// general step (lane_slow_step: seed and close matches, deferred anchors, long extensions, the tail) or for the
+// seed scan of a window no record describes (lane_scan_step).  The warp enters such a step only once
+// LZ_LANE_PARK_SLOW / LZ_LANE_PARK_SCAN lanes have a pair waiting for it (or nobody can run, or LZ_LANE_WAIT rounds
+// have passed), so the expensive code runs with many active lanes -- and because a lane holds several pairs it
+// usually still has a runnable one meanwhile.  Lanes pull new pairs as theirs finish (consecutive pairs of a
+// chunk share their reference); a pair that lives in the general code (related genomes: hundreds of seed / close
+// matches) is handed to the warp-per-pair walk, which does those steps 32 lanes wide.
+constexpr int LANE_EMPTY = 4;            // slot without a pair (the chunk has run out)
+constexpr int LANE_CTX_WORDS = 21;
+struct LaneSlots {
+    uint32_t w[LZ_LANE_SLOTS][LANE_CTX_WORDS][LZ_LANE_THREADS];
+};
+__device__ __forceinline__ void lane_ctx_store(LaneSlots& m, int j, const LaneCtx& L, uint32_t r0, uint32_t pl, int parks)
 {
-    lane_slow_step(L, P);
-    return L;
+    uint32_t (*w)[LZ_LANE_THREADS] = m.w[j];
+    const int t = threadIdx.x;
+    w[0][t] = r0; w[1][t] = L.n; w[2][t] = L.c; w[3][t] = (uint32_t)L.n_loop;
+    w[4][t] = (uint32_t)L.s.i; w[5][t] = (uint32_t)L.s.pred; w[6][t] = (uint32_t)L.s.lit;
+    w[7][t] = (uint32_t)L.s.rs; w[8][t] = (uint32_t)L.s.re; w[9][t] = (uint32_t)L.s.kept_end;
+    w[10][t] = (uint32_t)L.s.curM; w[11][t] = (uint32_t)L.s.curX;
+    w[12][t] = (uint32_t)L.s.totM; w[13][t] = (uint32_t)L.s.totX; w[14][t] = (uint32_t)L.s.totN;
+    w[15][t] = (uint32_t)L.spec_K1; w[16][t] = (uint32_t)L.spec_ks; w[17][t] = (uint32_t)L.spec_x;
+    w[18][t] = (uint32_t)parks; w[19][t] = pl; w[20][t] = (uint32_t)L.chain;
 }
-template <class PT>
-__device__ LZ_LANE_SLOW_ATTR LaneCtx lane_scan_call(LaneCtx L, PT P)
+__device__ __forceinline__ void lane_ctx_load(const LaneSlots& m, int j, LaneCtx& L, const Rec* hit_recs, uint32_t& r0, uint32_t& pl,
+                                              int& parks, int mode)
 {
-    lane_scan_step(L, P);
-    return L;
+    const uint32_t (*w)[LZ_LANE_THREADS] = m.w[j];
+    const int t = threadIdx.x;
+    r0 = w[0][t]; L.recs = hit_recs + r0; L.n = w[1][t]; L.c = w[2][t]; L.n_loop = (int)w[3][t];
+    L.s.i = (int)w[4][t]; L.s.pred = (int)w[5][t]; L.s.lit = (int)w[6][t];
+    L.s.rs = (int)w[7][t]; L.s.re = (int)w[8][t]; L.s.kept_end = (int)w[9][t];
+    L.s.curM = (int)w[10][t]; L.s.curX = (int)w[11][t];
+    L.s.totM = (int)w[12][t]; L.s.totX = (int)w[13][t]; L.s.totN = (int)w[14][t];
+    L.spec_K1 = (int)w[15][t]; L.spec_ks = (int)w[16][t]; L.spec_x = (int)w[17][t];
+    parks = (int)w[18][t]; pl = w[19][t]; L.chain = (int)w[20][t];
+    L.mode = mode;
 }
 
 template <class PT>
@@ -491,54 +513,113 @@ k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
              uint64_t pair_begin, PT P, const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
              int3* __restrict__ out, uint32_t* __restrict__ hard_list, unsigned long long* __restrict__ hard_count)
 {
-    LaneCtx L;
-    L.mode = LANE_DONE;
-    uint32_t pl = 0xFFFFFFFFu;
+    __shared__ LaneSlots slots;
+    int mode[LZ_LANE_SLOTS];
+#pragma unroll
+    for (int j = 0; j < LZ_LANE_SLOTS; ++j) mode[j] = LANE_DONE;
     bool more = true;
-    int w_slow = 0, w_scan = 0;           // rounds the parked lanes have waited
-    int parks = 0, park_limit = 0;        // parked steps of this lane's pair; beyond the limit the pair is handed over
+    int w_slow = 0, w_scan = 0;           // rounds the parked pairs have waited
     for (;;) {
-        if (L.mode == LANE_DONE) {
-            if (pl != 0xFFFFFFFFu) {
-                out[pair_begin + pl] = make_int3(L.s.totM, L.s.totX, L.s.totN);
-                pl = 0xFFFFFFFFu;
+        // ---- new pairs into the slots whose pair is done
+        bool live = false;
+#pragma unroll
+        for (int j = 0; j < LZ_LANE_SLOTS; ++j) {
+            if (mode[j] == LANE_DONE) {
+                mode[j] = LANE_EMPTY;
+                if (more) {
+                    const unsigned long long k = atomicAdd(counter, 1ull);
+                    if (k < n_pairs) {
+                        const uint32_t pl = (uint32_t)k;
+                        const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
+                        LaneCtx L;
+                        PairView pv{};
+                        pv.Dq = desc[pl].Dq;
+                        lane_begin(L, pv, hit_recs + r0, r1 - r0, P.msl);
+                        lane_ctx_store(slots, j, L, r0, pl, 0);
+                        mode[j] = LANE_RUN;
+                    } else more = false;
+                }
             }
-            if (more) {
-                const unsigned long long k = atomicAdd(counter, 1ull);
-                if (k < n_pairs) {
-                    pl = (uint32_t)k;
-                    const PairView pv = view_of(desc[pl], recs, nullptr, table_pool);
-                    const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
-                    lane_begin(L, pv, hit_recs + r0, r1 - r0, P.msl);
-                    parks = 0;
-                    park_limit = LZ_LANE_HARD_BASE + (L.n_loop >> LZ_LANE_HARD_SHIFT);
-                } else more = false;
-            }
+            live = live || mode[j] != LANE_EMPTY;
         }
-        if (!__any_sync(0xFFFFFFFFu, L.mode != LANE_DONE)) return;
+        if (!__any_sync(0xFFFFFFFFu, live)) return;
+
+        // ---- plain events of one runnable pair
+        int jr = -1, js = -1, jc = -1;
+#pragma unroll
+        for (int j = LZ_LANE_SLOTS - 1; j >= 0; --j) if (mode[j] == LANE_RUN) jr = j;
+        if (jr >= 0) {
+            LaneCtx L;
+            uint32_t r0, pl;
+            int parks;
+            lane_ctx_load(slots, jr, L, hit_recs, r0, pl, parks, LANE_RUN);
+            RecAhead ahead;
+            ahead.base = L.c;
+#pragma unroll
+            for (uint32_t k = 0; k < 4u; ++k) {
+                ahead.r[k] = Rec{0x7FFFFFFFu, 0, 0, 0};
+                if (L.c + k < L.n) ahead.r[k] = ld_rec(L.recs + L.c + k);
+            }
 #pragma unroll 1
-        for (int r = 0; r < LZ_LANE_RUN_STEPS; ++r)
-            if (L.mode == LANE_RUN) lane_run_step(L, P);
+            for (int r = 0; r < LZ_LANE_RUN_STEPS && L.mode == LANE_RUN; ++r) lane_run_step(L, P, ahead);
+            lane_ctx_store(slots, jr, L, r0, pl, parks);
+#pragma unroll
+            for (int j = 0; j < LZ_LANE_SLOTS; ++j) if (j == jr) mode[j] = L.mode;
+        }
         __syncwarp();
-        bool any_run = __any_sync(0xFFFFFFFFu, L.mode == LANE_RUN);
-        const int n_slow = __popc(__ballot_sync(0xFFFFFFFFu, L.mode == LANE_SLOW));
+        bool has_run = false;
+#pragma unroll
+        for (int j = LZ_LANE_SLOTS - 1; j >= 0; --j) {
+            has_run = has_run || mode[j] == LANE_RUN;
+            if (mode[j] == LANE_SLOW) js = j;
+        }
+        bool any_run = __any_sync(0xFFFFFFFFu, has_run);
+
+        // ---- the general step for the pairs waiting for it
+        const int n_slow = __popc(__ballot_sync(0xFFFFFFFFu, js >= 0));
         if (n_slow && (n_slow >= LZ_LANE_PARK_SLOW || !any_run || ++w_slow >= LZ_LANE_WAIT)) {
-            if (L.mode == LANE_SLOW) {
-                if (++parks > park_limit && L.s.i < L.n_loop) {
-                    // a pair that lives in the general code (related genomes: hundreds of seed / close matches): the
-                    // warp-per-pair walk does those steps 32 lanes wide -- hand the pair over (k_walk_pairs restarts it)
-                    hard_list[atomicAdd(hard_count, 1ull)] = pl;
-                    pl = 0xFFFFFFFFu;
+            if (js >= 0) {
+                LaneCtx L;
+                uint32_t r0, pl;
+                int parks;
+                lane_ctx_load(slots, js, L, hit_recs, r0, pl, parks, LANE_SLOW);
+                if (++parks > LZ_LANE_HARD_BASE + (L.n_loop >> LZ_LANE_HARD_SHIFT) && L.s.i < L.n_loop) {
+                    hard_list[atomicAdd(hard_count, 1ull)] = pl;       // k_walk_pairs restarts it
                     L.mode = LANE_DONE;
-                } else L = lane_slow_call(L, P);
+                } else {
+                    L.pv = view_of(desc[pl], recs, nullptr, table_pool);
+                    lane_slow_step(L, P);
+                    if (L.mode == LANE_DONE) out[pair_begin + pl] = make_int3(L.s.totM, L.s.totX, L.s.totN);
+                    else lane_ctx_store(slots, js, L, r0, pl, parks);
+                }
+#pragma unroll
+                for (int j = 0; j < LZ_LANE_SLOTS; ++j) if (j == js) mode[j] = L.mode;
             }
             __syncwarp();
             w_slow = 0;
-            any_run = __any_sync(0xFFFFFFFFu, L.mode == LANE_RUN);
+            has_run = false;
+#pragma unroll
+            for (int j = 0; j < LZ_LANE_SLOTS; ++j) has_run = has_run || mode[j] == LANE_RUN;
+            any_run = __any_sync(0xFFFFFFFFu, has_run);
         }
-        const int n_scan = __popc(__ballot_sync(0xFFFFFFFFu, L.mode == LANE_SCAN));
+
+        // ---- the seed scan for the pairs waiting for it
+#pragma unroll
+        for (int j = LZ_LANE_SLOTS - 1; j >= 0; --j) if (mode[j] == LANE_SCAN) jc = j;
+        const int n_scan = __popc(__ballot_sync(0xFFFFFFFFu, jc >= 0));
         if (n_scan && (n_scan >= LZ_LANE_PARK_SCAN || !any_run || ++w_scan >= LZ_LANE_WAIT)) {
-            if (L.mode == LANE_SCAN) { ++parks; L = lane_scan_call(L, P); }
+            if (jc >= 0) {
+                LaneCtx L;
+                uint32_t r0, pl;
+                int parks;
+                lane_ctx_load(slots, jc, L, hit_recs, r0, pl, parks, LANE_SCAN);
+                ++parks;
+                L.pv = view_of(desc[pl], recs, nullptr, table_pool);
+                lane_scan_step(L, P);
+                lane_ctx_store(slots, jc, L, r0, pl, parks);
+#pragma unroll
+                for (int j = 0; j < LZ_LANE_SLOTS; ++j) if (j == jc) mode[j] = L.mode;
+            }
             __syncwarp();
             w_scan = 0;
         }

@@ -20,25 +20,28 @@
 #ifndef LZ_WALK_MIN_BLOCKS
 #define LZ_WALK_MIN_BLOCKS 5
 #endif
-// lane-per-pair walk (k_walk_lanes): block size, resident blocks, plain events per round, parked lanes that
-// trigger the general step / the seed scan, rounds a parked lane waits at most
+// lane-per-pair walk (k_walk_lanes): block size, resident blocks, pairs per lane, plain events per round, lanes with
+// a waiting pair that trigger the general step / the seed scan, rounds a waiting pair waits at most
 #ifndef LZ_LANE_THREADS
 #define LZ_LANE_THREADS 128
 #endif
 #ifndef LZ_LANE_MIN_BLOCKS
 #define LZ_LANE_MIN_BLOCKS 4
 #endif
+#ifndef LZ_LANE_SLOTS
+#define LZ_LANE_SLOTS 3
+#endif
 #ifndef LZ_LANE_RUN_STEPS
-#define LZ_LANE_RUN_STEPS 4
+#define LZ_LANE_RUN_STEPS 8
 #endif
 #ifndef LZ_LANE_PARK_SLOW
-#define LZ_LANE_PARK_SLOW 12
+#define LZ_LANE_PARK_SLOW 24
 #endif
 #ifndef LZ_LANE_PARK_SCAN
-#define LZ_LANE_PARK_SCAN 16
+#define LZ_LANE_PARK_SCAN 24
 #endif
 #ifndef LZ_LANE_WAIT
-#define LZ_LANE_WAIT 8
+#define LZ_LANE_WAIT 32
 #endif
 // a lane hands its pair to the warp-per-pair walk after BASE + (query positions >> SHIFT) parked steps (an unrelated
 // 50 kb pair parks ~120 times, a related one 600-1300 times)
@@ -47,9 +50,6 @@
 #endif
 #ifndef LZ_LANE_HARD_SHIFT
 #define LZ_LANE_HARD_SHIFT 8
-#endif
-#ifndef LZ_LANE_SLOW_ATTR
-#define LZ_LANE_SLOW_ATTR __forceinline__
 #endif
 #ifndef LZ_RECORD_THREADS
 #define LZ_RECORD_THREADS 256

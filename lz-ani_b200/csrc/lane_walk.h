@@ -46,6 +46,8 @@ struct LaneCtx {
     int n_loop;                  // the loop of parser.cpp:501 runs while i < n_loop = Dq - msl
     ParseState s;
     int spec_K1, spec_ks, spec_x;    // speculative seed record of the match just taken (spec_K1 > 0 <=> valid for the window at s.i)
+    int chain;                   // verified successor link of the record just taken (0: none): the next event is the
+                                 // record that many places on, plain, whatever the region bookkeeping says (verified_link)
     int mode;
 };
 
@@ -59,6 +61,7 @@ LZ_HD void lane_begin(LaneCtx& L, const PairView& pv, const Rec* recs, uint32_t 
     L.s.curM = L.s.curX = 0;
     L.s.totM = L.s.totX = L.s.totN = 0;
     L.spec_K1 = 0; L.spec_ks = 64; L.spec_x = -1;
+    L.chain = 0;
     L.mode = LANE_RUN;
 }
 
@@ -304,13 +307,13 @@ inline int lane_check_first_seed(const PairView& pv, const PT& P, int i0, int P0
 // ---- the next anchor event at or after query position i0 and below lim (next_event(), one lane): the first
 // record that is not behind the walk and either counts itself or has a run of hits reaching i0 ("virtual":
 // LIVE | DEFER, evaluated by anchor_lookup_lane when taken).  Advances the cursor over records behind i0.
-struct LaneEvent { int qi, a_pos; uint32_t w2, w3, idx; };
+struct LaneEvent { int qi, a_pos; uint32_t w2, w3, idx, link; };
 LZ_HD int rec_pos(const Rec& h) { return (int)(h.x & (uint32_t)(LZ_STAGED_MAX_POS - 1)); }
 LZ_HD int rec_run(const Rec& h) { return (int)((h.z >> HIT_RUN_SHIFT) & 7u); }
 LZ_HD LaneEvent lane_next_event(LaneCtx& L, int i0, int lim, bool need_pos)
 {
     LaneEvent o;
-    o.qi = LANE_NONE; o.a_pos = 0; o.w2 = 0; o.w3 = 0; o.idx = L.n;
+    o.qi = LANE_NONE; o.a_pos = 0; o.w2 = 0; o.w3 = 0; o.idx = L.n; o.link = 0;
     uint32_t c = L.c;
     bool behind_prefix = true;
     int skipped = 0;
@@ -346,7 +349,7 @@ LZ_HD LaneEvent lane_next_event(LaneCtx& L, int i0, int lim, bool need_pos)
         if (p >= lim) break;                    // position order: nothing else lies below lim either
         const bool counts = (h.z & HIT_LIVE) && (!need_pos || (h.z & HIT_DEFER) || h.y != 0u);
         if (p >= i0 && counts) {
-            o.qi = p; o.a_pos = (int)h.y; o.w2 = h.z; o.w3 = h.w; o.idx = c;
+            o.qi = p; o.a_pos = (int)h.y; o.w2 = h.z; o.w3 = h.w; o.idx = c; o.link = h.x >> HIT_ENTRY_RUN_SHIFT;
             break;
         }
         if (run > 0) {                          // the walk stands inside the run, or the run's first hit does not count
@@ -460,14 +463,85 @@ LZ_HD void lane_set_spec(LaneCtx& L, uint32_t w2, uint32_t w3)
 #else
 #define LZ_LANE_WHY(n)
 #endif
+// the records [base, base + 4) of the pair, loaded together ahead of the steps that will want them (the kernel
+// issues the four loads at once: one memory latency per round instead of one per step)
+struct RecAhead {
+    Rec r[4];
+    uint32_t base;
+};
+LZ_HD Rec rec_ahead_get(const RecAhead& a, uint32_t k)      // k < 4; selects, not an indexed (local-memory) access
+{
+    Rec h = a.r[0];
+    if (k == 1u) h = a.r[1];
+    if (k == 2u) h = a.r[2];
+    if (k == 3u) h = a.r[3];
+    return h;
+}
+
 template <class PT>
-LZ_HD void lane_run_step(LaneCtx& L, const PT& P)
+LZ_HD void lane_run_step(LaneCtx& L, const PT& P, const RecAhead& ahead)
 {
     ParseState& s = L.s;
+    if (L.chain) {
+        // ---- chained event (62 % of the events of an unrelated pair): the record just taken carries a verified link,
+        // so the next event is that record, a distant match taken from its fields -- nothing to decide
+        const uint32_t idx = L.c - 1u + (uint32_t)L.chain;
+        const uint32_t ka = idx - ahead.base;
+        const Rec h = ka < 4u ? rec_ahead_get(ahead, ka) : ld_rec(L.recs + idx);
+        const int qi = rec_pos(h), a_pos = (int)h.y;
+        const uint32_t w2 = h.z, w3 = h.w;
+#if defined(LZ_SPEC_CHECK) && !defined(__CUDA_ARCH__)
+        {   // TEST ONLY (tests/emul): the general rules must find the same event, plain, with a usable backward record
+            LaneCtx G = L;
+            const LaneEvent e2 = lane_next_event(G, s.i, LANE_NONE, false);
+            bool ok = e2.idx == idx && e2.qi == qi && (w2 & (HIT_LIVE | HIT_DEFER | HIT_FWD | HIT_BWD)) == (HIT_LIVE | HIT_FWD | HIT_BWD) &&
+                      s.pred >= 0 && L.spec_K1 > 0;
+            const int kq = qi - s.i;
+            if (kq > P.mqd) ok = ok && L.spec_K1 > P.mqd && L.spec_ks >= 64;
+            else {
+                int dist = a_pos - (s.pred + kq);
+                if (dist < 0) dist = -dist;
+                ok = ok && kq < L.spec_K1 && L.spec_ks > kq && a_pos != 0 && dist > P.mrd;
+            }
+            const bool keep2 = s.rs >= 0 && s.re - s.rs >= P.reg;
+            const int run2 = qi - (keep2 ? s.re : s.kept_end);
+            int lim2 = run2 < qi ? run2 : qi;
+            if (a_pos < lim2) lim2 = a_pos;
+            ok = ok && run2 > 0 && lim2 >= (int)((w3 >> 12) & 63u);
+            if (!ok) { lz_spec_mismatches++; fprintf(stderr, "DBG chain: i %d qi %d idx %u/%u\n", s.i, qi, idx, e2.idx); }
+            lz_chain++; lz_fast++;
+        }
+#endif
+        if (s.re - s.rs >= P.reg) { s.totM += s.curM; s.totX += s.curX; ++s.totN; s.kept_end = s.re; }
+        const int len = (int)(w2 & 63u), fwd = (int)((w2 >> 6) & 63u), fm = (int)((w2 >> 12) & 63u);
+        const int back = (int)(w3 & 63u), bm = (int)((w3 >> 6) & 63u);
+        s.curM = bm + len + fm;
+        s.curX = back - bm + fwd - fm;
+        s.rs = qi - back;
+        s.i = qi + len + fwd;
+        s.pred = a_pos + len + fwd;
+        s.re = s.i;
+        lane_set_spec(L, w2, w3);
+        L.chain = (int)(h.x >> HIT_ENTRY_RUN_SHIFT);
+        L.c = idx + 1u;
+        return;
+    }
     const int i0 = s.i;
     if (i0 >= L.n_loop) { LZ_LANE_WHY(0); L.mode = LANE_SLOW; return; }                   // the tail
     if (s.pred >= 0 && L.spec_K1 <= 0) { LZ_LANE_WHY(1); L.mode = LANE_SCAN; return; }     // a window nobody has scanned
-    const LaneEvent ev = lane_next_event(L, i0, LANE_NONE, false);
+    // the next anchor event: nearly always the record under the cursor itself (one load, no search)
+    LaneEvent ev;
+    bool direct = false;
+    if (L.c < L.n) {
+        const uint32_t ka = L.c - ahead.base;
+        const Rec h = ka < 4u ? rec_ahead_get(ahead, ka) : ld_rec(L.recs + L.c);
+        const int p = rec_pos(h);
+        if (p >= i0 && (h.z & HIT_LIVE)) {
+            ev.qi = p; ev.a_pos = (int)h.y; ev.w2 = h.z; ev.w3 = h.w; ev.idx = L.c; ev.link = h.x >> HIT_ENTRY_RUN_SHIFT;
+            direct = true;
+        }
+    }
+    if (!direct) ev = lane_next_event(L, i0, LANE_NONE, false);
     const int qi = ev.qi;
     const uint32_t w2 = ev.w2, w3 = ev.w3;
     const int a_pos = ev.a_pos;
@@ -541,6 +615,8 @@ LZ_HD void lane_run_step(LaneCtx& L, const PT& P)
             s.re = s.i;
             lane_set_spec(L, w2, w3);
             L.c = ev.idx + 1u;
+            // (run > 0: the region just opened is the one the record's fields describe -- what verified_link assumed)
+            if (run > 0 && L.spec_K1 > 0) L.chain = (int)ev.link;
             return;
         }
         LZ_LANE_WHY(5);
@@ -594,6 +670,7 @@ LZ_HD void lane_slow_step(LaneCtx& L, const PT& P)
     ParseState& s = L.s;
     const PairView& pv = L.pv;
     const int i0 = s.i;
+    L.chain = 0;
     if (i0 >= L.n_loop) { lane_finish(L, P); return; }
     if (s.pred >= 0 && L.spec_K1 <= 0) { L.mode = LANE_SCAN; return; }
     L.mode = LANE_RUN;
@@ -725,8 +802,11 @@ LZ_HD PairResult lane_walk_pair(const PairView& pv, const PT& P, const Rec* recs
 {
     LaneCtx L;
     lane_begin(L, pv, recs, n_recs, P.msl);
+    RecAhead none;
+    none.base = 0x80000000u;     // no record index comes within 4 of it
+    for (int k = 0; k < 4; ++k) none.r[k] = Rec{0, 0, 0, 0};
     while (L.mode != LANE_DONE) {
-        if (L.mode == LANE_RUN) lane_run_step(L, P);
+        if (L.mode == LANE_RUN) lane_run_step(L, P, none);
         else if (L.mode == LANE_SCAN) lane_scan_step(L, P);
         else lane_slow_step(L, P);
     }
