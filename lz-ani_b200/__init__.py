@@ -98,14 +98,18 @@ class Matcher:
     """Mirror of what CLZMatcher::do_matching does with its CParser objects
     (reference src/lz_matcher.cpp:172-277), batch form."""
 
-    def __init__(self, params: dict | None = None, device: int | None = None):
+    def __init__(self, params: dict | None = None, device: int | None = None, devices=None):
+        """device: one GPU.  devices=[d0, d1, ...]: ONE context driving several GPUs -- the library owns the devices
+        and deals the reference rows over them (lzani_create with n_devices > 1)."""
         self.lib = load_library()
         self.params = hostio.params_array(params)
         self.h = C.c_void_p()
-        dev = None
-        if device is not None:
-            dev = (C.c_int * 1)(int(device))
-        rc = self.lib.lzani_create(C.byref(self.h), self.params.ctypes.data, dev, 1 if device is not None else 0)
+        dev, n_dev = None, 0
+        if devices is not None:
+            dev, n_dev = (C.c_int * len(devices))(*[int(d) for d in devices]), len(devices)
+        elif device is not None:
+            dev, n_dev = (C.c_int * 1)(int(device)), 1
+        rc = self.lib.lzani_create(C.byref(self.h), self.params.ctypes.data, dev, n_dev)
         if rc != 0:
             msg = self.lib.lzani_last_error(self.h).decode() if self.h else "allocation failed"
             if self.h:

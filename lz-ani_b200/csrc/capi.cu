@@ -11,6 +11,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/lzani_b200.h"
@@ -20,6 +21,10 @@ using namespace lzani;
 
 struct lzani_ctx {
     Prm P{};
+    // n_devices > 1 at lzani_create: this object is the GROUP -- one full single-device context per GPU in `subs`, driven by
+    // worker threads the library spawns per call (the reference's own thread pool, lz_matcher.cpp:184-200, is inside
+    // do_matching too); reference rows are dealt over the devices, sequences replicated, no collective.
+    std::vector<lzani_ctx*> subs;
     int device = -1;
     int n_sm = 0;
     int blocks_per_sm = 1;
@@ -193,8 +198,18 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     if (!c) return LZANI_ERR_NOMEM;
     *out = c;
     if (!p) return fail(c, LZANI_ERR_ARG, "params == NULL");
-    if (n_devices > 1) return fail(c, LZANI_ERR_ARG, "one context drives one GPU: n_devices must be 1 (use one process per GPU)");
     c->P = Prm{p->mal, p->msl, p->mrd, p->mqd, p->reg, p->aw, p->am, p->ar};
+    if (n_devices > 1) {
+        if (!device_ids) return fail(c, LZANI_ERR_ARG, "device_ids == NULL with n_devices > 1");
+        // (a device may be named twice: two contexts sharing one GPU -- how the group path is tested on a one-GPU box)
+        for (int g = 0; g < n_devices; ++g) {
+            lzani_ctx* sub = nullptr;
+            const int rc = lzani_create(&sub, p, device_ids + g, 1);
+            if (sub) c->subs.push_back(sub);
+            if (rc != LZANI_OK) return fail(c, rc, "device " + std::to_string(device_ids[g]) + ": " + (sub ? sub->err : std::string("allocation failed")));
+        }
+        return LZANI_OK;
+    }
     const Prm& P = c->P;
     // what the kernels support (the reference has no explicit limits except mal <= 32, parser.cpp:59)
     if (P.mal < 1 || P.mal > 32) return fail(c, LZANI_ERR_ARG, "mal must be in [1,32]");
@@ -240,7 +255,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
         LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
-        LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, sizeof(uint32_t)));
+        LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, 4 * sizeof(uint32_t)));
         LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, 4 * sizeof(unsigned long long)));
     }
     return LZANI_OK;
@@ -249,6 +264,8 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
 extern "C" void lzani_destroy(lzani_ctx* c)
 {
     if (!c) return;
+    for (lzani_ctx* sub : c->subs) lzani_destroy(sub);
+    c->subs.clear();
     if (c->device >= 0) {
         cudaSetDevice(c->device);
         free_sequences(c);
@@ -278,6 +295,7 @@ extern "C" int lzani_set_index_budget(lzani_ctx* c, uint64_t bytes)
 {
     if (!c) return LZANI_ERR_ARG;
     c->budget = bytes;
+    for (lzani_ctx* sub : c->subs) sub->budget = bytes;       // per device
     return LZANI_OK;
 }
 
@@ -290,15 +308,55 @@ extern "C" int lzani_get_timing(const lzani_ctx* c, lzani_timing_t* t)
 
 namespace {
 int set_sequences_impl(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len, bool ascii);
+
+// ---- group plumbing: f(g, sub) on every device of the group, one host thread each; the first error wins
+template <class F>
+int group_each(lzani_ctx* c, F f)
+{
+    const size_t G = c->subs.size();
+    std::vector<int> rc(G, LZANI_OK);
+    std::vector<std::thread> th;
+    for (size_t g = 1; g < G; ++g) th.emplace_back([&, g] { rc[g] = f((uint32_t)g, c->subs[g]); });
+    rc[0] = f(0u, c->subs[0]);
+    for (auto& t : th) t.join();
+    for (size_t g = 0; g < G; ++g)
+        if (rc[g] != LZANI_OK) return fail(c, rc[g], "device " + std::to_string(c->subs[g]->device) + ": " + c->subs[g]->err);
+    return LZANI_OK;
 }
+// timings of a group call: the devices run side by side -- times are the slowest device's, counts add up
+void group_timing(lzani_ctx* c)
+{
+    lzani_timing_t T{};
+    for (const lzani_ctx* s : c->subs) {
+        const lzani_timing_t& t = s->timing;
+        T.h2d_ms = std::max(T.h2d_ms, t.h2d_ms); T.pack_ms = std::max(T.pack_ms, t.pack_ms);
+        T.index_ms = std::max(T.index_ms, t.index_ms); T.parse_ms = std::max(T.parse_ms, t.parse_ms);
+        T.d2h_ms = std::max(T.d2h_ms, t.d2h_ms); T.total_ms = std::max(T.total_ms, t.total_ms);
+        T.filter_ms = std::max(T.filter_ms, t.filter_ms); T.pairlist_ms = std::max(T.pairlist_ms, t.pairlist_ms);
+        T.n_pairs += t.n_pairs; T.q_bases += t.q_bases; T.r_bases += t.r_bases;
+        T.h2d_bytes += t.h2d_bytes; T.d2h_bytes += t.d2h_bytes; T.filter_d2h_bytes += t.filter_d2h_bytes;
+        T.launches += t.launches; T.n_batches = std::max(T.n_batches, t.n_batches);
+    }
+    c->timing = T;
+}
+int group_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len, bool ascii)
+{
+    const int rc = group_each(c, [&](uint32_t, lzani_ctx* s) { return set_sequences_impl(s, n, data, len, ascii); });
+    c->n_seqs = rc == LZANI_OK ? n : 0;
+    group_timing(c);
+    return rc;
+}
+}  // namespace
 
 extern "C" int lzani_set_sequences(lzani_ctx* c, uint32_t n, const uint8_t* const* data, const uint32_t* len)
 {
+    if (c && !c->subs.empty()) return group_set_sequences(c, n, data, len, false);
     return set_sequences_impl(c, n, data, len, false);
 }
 
 extern "C" int lzani_set_sequences_text(lzani_ctx* c, uint32_t n, const uint8_t* const* text, const uint32_t* len)
 {
+    if (c && !c->subs.empty()) return group_set_sequences(c, n, text, len, true);
     return set_sequences_impl(c, n, text, len, true);
 }
 
@@ -413,7 +471,6 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
     if (!c->d_recs) return fail(c, LZANI_ERR_STATE, "lzani_set_sequences has not been called");
     if (q_ids && !row_off_in) return fail(c, LZANI_ERR_ARG, "q_ids given without row_off");
-    if (copy_out && !out) return fail(c, LZANI_ERR_ARG, "out == NULL");
     if (repeat < 1) repeat = 1;
     LZ_CUDA(c, cudaSetDevice(c->device));
     const Prm& P = c->P;
@@ -437,6 +494,9 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         }
     }
     const uint64_t n_pairs = row_off[n_rows];
+    // (a submit without pairs -- a single sequence, a filter nothing passes, a GPU whose rows are empty -- is legal and
+    // returns nothing: the reference writes header-only output then)
+    if (copy_out && !out && n_pairs) return fail(c, LZANI_ERR_ARG, "out == NULL");
     const uint32_t* q_src = q_ids ? q_ids + row_off_in[0] : nullptr;
     c->last_valid = false;
     bool rows_sorted = true;
@@ -685,15 +745,27 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                                                   c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, ch.k0, (uint32_t)np,
                                                   ch.words, P, c->d_bitmap, c->n_sm, use_mx ? &mx : nullptr));
                     LZ_CUDA(c, cudaMemcpyAsync(sl.h_total, sl.B.rec_off + ch.words, sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.st));
+                    // rec_off is a 32-bit scan: a word holds up to 16 hit runs, so beyond 2^28 words the total could wrap --
+                    // such chunks also get the exact 64-bit count (one more pass over the hit masks, ~0.5 ms)
+                    const bool may_wrap = ch.words * 16ull >= (1ull << 32);
+                    if (may_wrap) {
+                        LZ_CUDA(c, launch_run_total(sl.st, sl.B, ch.words));
+                        LZ_CUDA(c, cudaMemcpyAsync(sl.h_total + 2, sl.B.counter + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, sl.st));
+                    }
                     LZ_CUDA(c, cudaStreamSynchronize(sl.st));
-                    const uint64_t n_hit = *sl.h_total;
+                    uint64_t n_hit = *sl.h_total;
+                    if (may_wrap) {
+                        unsigned long long exact;
+                        memcpy(&exact, sl.h_total + 2, sizeof(exact));
+                        n_hit = exact;
+                    }
                     T.launches += 1 + (ch.words ? (use_mx ? 2 * ((mx.n_rows_chunk + 31) / 32) : 1) : 0);     // our kernels (CUB's scans not counted)
                     if (ch.words) {
                         const double ratio = (double)n_hit / (double)ch.words;
                         c->rec_per_word = ratio > c->rec_per_word ? ratio : 0.5 * (c->rec_per_word + ratio);
                         if (c->rec_per_word < 0.25) c->rec_per_word = 0.25;
                     }
-                    if (n_hit > sl.recs_cap) {
+                    if (n_hit > sl.recs_cap || n_hit > 0xFFFFFFFFull) {
                         if (np > 1) {                      // too many hit runs for the record buffers: halve the chunk
                             const uint64_t mid = ch.k0 + np / 2;
                             const uint64_t w0 = range_words(ch.k0, mid);
@@ -701,6 +773,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                             redo.push_back(Range{ch.k0, mid, w0});
                             continue;
                         }
+                        if (n_hit > 0xFFFFFFFFull) return fail(c, LZANI_ERR_NOMEM, "one pair has more than 2^32 hit runs");
                         if (int rc = ensure_slot(c, sl, sl.pairs_cap, sl.words_cap, n_hit)) return rc;
                     }
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
@@ -776,10 +849,167 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
 
 }  // namespace
 
+namespace {
+
+// ---- a run on a group: the rows are dealt over the devices (dense rows: row j -> device j mod G, every device gets the
+// same length mix of the length-sorted ids; sparse rows: heaviest first onto the least loaded device, by query bases),
+// every device parses its rows (run_rows_impl, its own host thread), and each worker scatters its results into the
+// caller's CSR order.  No collective: the only shared data are the read-only sequences, replicated at set_sequences.
+int group_run_rows(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off_in, const uint32_t* q_ids,
+                   int repeat, lzani_result_t* out, bool copy_out, const RegionReq* rq = nullptr)
+{
+    const uint32_t G = (uint32_t)c->subs.size();
+    const uint32_t n = c->n_seqs;
+    if (q_ids && !row_off_in) return fail(c, LZANI_ERR_ARG, "q_ids given without row_off");
+    if (copy_out && !out) {
+        bool any = false;
+        if (q_ids) any = row_off_in[n_rows] > row_off_in[0]; else any = n_rows && n > 1;
+        if (any) return fail(c, LZANI_ERR_ARG, "out == NULL");
+    }
+    if (rq && (!rq->n_regions || (rq->cap && (!rq->regions || !rq->region_off)))) return fail(c, LZANI_ERR_ARG, "region buffers == NULL");
+    // global CSR offsets of the rows (relative to the first)
+    std::vector<uint64_t> goff((size_t)n_rows + 1, 0);
+    for (uint32_t j = 0; j < n_rows; ++j) {
+        if (q_ids) {
+            if (row_off_in[j + 1] < row_off_in[j]) return fail(c, LZANI_ERR_ARG, "row_off is not non-decreasing");
+            goff[j + 1] = row_off_in[j + 1] - row_off_in[0];
+        } else goff[j + 1] = goff[j] + (n ? n - 1 : 0);
+    }
+    const uint32_t* q_src = q_ids ? q_ids + row_off_in[0] : nullptr;
+    std::vector<uint32_t> owner(n_rows);
+    if (!q_ids) for (uint32_t j = 0; j < n_rows; ++j) owner[j] = j % G;
+    else {
+        const lzani_ctx* s0 = c->subs[0];
+        std::vector<uint64_t> cost(n_rows, 0), load(G, 0);
+        for (uint32_t j = 0; j < n_rows; ++j)
+            for (uint64_t k = goff[j]; k < goff[j + 1]; ++k) {
+                if (q_src[k] >= n) return fail(c, LZANI_ERR_ARG, "query id out of range");
+                cost[j] += s0->meta[q_src[k]].len;
+            }
+        std::vector<uint32_t> order(n_rows);
+        for (uint32_t j = 0; j < n_rows; ++j) order[j] = j;
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
+        for (uint32_t j : order) {
+            const uint32_t g = (uint32_t)(std::min_element(load.begin(), load.end()) - load.begin());
+            owner[j] = g;
+            load[g] += cost[j] + 1;
+        }
+    }
+    struct Part {
+        std::vector<uint32_t> rows_local, refs, q;
+        std::vector<uint64_t> off;
+        std::vector<lzani_result_t> res;
+        std::vector<uint64_t> region_off;
+        std::vector<lzani_region_t> regions;
+        uint64_t n_regions = 0;
+    };
+    std::vector<Part> part(G);
+    for (uint32_t g = 0; g < G; ++g) part[g].off.assign(1, 0);
+    for (uint32_t j = 0; j < n_rows; ++j) {
+        Part& pt = part[owner[j]];
+        pt.rows_local.push_back(j);
+        pt.refs.push_back(ref_ids ? ref_ids[j] : j);
+        if (q_ids) pt.q.insert(pt.q.end(), q_src + goff[j], q_src + goff[j + 1]);
+        pt.off.push_back(pt.off.back() + (goff[j + 1] - goff[j]));
+    }
+    const int rc = group_each(c, [&](uint32_t g, lzani_ctx* s) {
+        Part& pt = part[g];
+        const uint64_t np = pt.off.back();
+        if (copy_out) pt.res.resize(np);
+        int r;
+        if (rq) {
+            pt.region_off.assign(np + 1, 0);
+            uint64_t cap = std::max<uint64_t>(1024, 4 * np);
+            for (;;) {
+                pt.regions.resize(cap);
+                const RegionReq sub_rq{pt.region_off.data(), pt.regions.data(), cap, &pt.n_regions};
+                r = run_rows_impl(s, (uint32_t)pt.refs.size(), pt.refs.data(), q_ids ? pt.off.data() : nullptr, q_ids ? pt.q.data() : nullptr,
+                                  repeat, pt.res.data(), copy_out, &sub_rq);
+                if (r == LZANI_ERR_NOMEM && pt.n_regions > cap) { cap = pt.n_regions + pt.n_regions / 8; continue; }
+                break;
+            }
+        } else
+            r = run_rows_impl(s, (uint32_t)pt.refs.size(), pt.refs.data(), q_ids ? pt.off.data() : nullptr, q_ids ? pt.q.data() : nullptr,
+                              repeat, copy_out ? pt.res.data() : nullptr, copy_out, nullptr);
+        if (r != LZANI_OK) return r;
+        if (copy_out)
+            for (size_t jl = 0; jl < pt.rows_local.size(); ++jl) {
+                const uint32_t j = pt.rows_local[jl];
+                if (goff[j + 1] > goff[j])
+                    memcpy(out + goff[j], pt.res.data() + pt.off[jl], sizeof(lzani_result_t) * (goff[j + 1] - goff[j]));
+            }
+        return (int)LZANI_OK;
+    });
+    group_timing(c);
+    if (rc != LZANI_OK) return rc;
+    if (rq) {
+        uint64_t total = 0;
+        for (const Part& pt : part) total += pt.n_regions;
+        *rq->n_regions = total;
+        if (total > rq->cap) return fail(c, LZANI_ERR_NOMEM, "regions buffer too small: " + std::to_string(total) + " regions");
+        // stitch the per-device region lists back into the caller's CSR order
+        const uint64_t np_all = goff[n_rows];
+        std::vector<uint64_t> cnt(np_all + 1, 0);
+        for (const Part& pt : part)
+            for (size_t jl = 0; jl < pt.rows_local.size(); ++jl) {
+                const uint32_t j = pt.rows_local[jl];
+                for (uint64_t k = 0; k < goff[j + 1] - goff[j]; ++k)
+                    cnt[goff[j] + k + 1] = pt.region_off[pt.off[jl] + k + 1] - pt.region_off[pt.off[jl] + k];
+            }
+        for (uint64_t k = 0; k < np_all; ++k) cnt[k + 1] += cnt[k];
+        for (const Part& pt : part)
+            for (size_t jl = 0; jl < pt.rows_local.size(); ++jl) {
+                const uint32_t j = pt.rows_local[jl];
+                const uint64_t a = pt.region_off[pt.off[jl]], b = pt.region_off[pt.off[jl + 1]];
+                if (b > a) memcpy(rq->regions + cnt[goff[j]], pt.regions.data() + a, sizeof(lzani_region_t) * (b - a));
+            }
+        memcpy(rq->region_off, cnt.data(), sizeof(uint64_t) * (np_all + 1));
+    }
+    return LZANI_OK;
+}
+
+int group_filter_pairs(lzani_ctx* c, const uint32_t* eff_len, const lzani_out_filter_t* flt, lzani_pair_t* pairs, uint64_t cap,
+                       uint64_t* n_out)
+{
+    if (!eff_len || !flt || !n_out || (cap && !pairs)) return fail(c, LZANI_ERR_ARG, "eff_len / flt / pairs / n_out == NULL");
+    const size_t G = c->subs.size();
+    std::vector<std::vector<lzani_pair_t>> sv(G);
+    const int rc = group_each(c, [&](uint32_t g, lzani_ctx* s) {
+        std::vector<lzani_pair_t>& v = sv[g];
+        v.resize(1024);
+        for (;;) {
+            uint64_t need = 0;
+            const int r = lzani_filter_pairs(s, c->subs.data(), (int)G, eff_len, flt, v.data(), v.size(), &need);
+            if (r == LZANI_ERR_NOMEM && need > v.size()) { v.resize(need); continue; }
+            if (r != LZANI_OK) return r;
+            v.resize(need);
+            return (int)LZANI_OK;
+        }
+    });
+    group_timing(c);
+    if (rc != LZANI_OK) return rc;
+    uint64_t total = 0;
+    for (const auto& v : sv) total += v.size();
+    *n_out = total;
+    if (total > cap) return fail(c, LZANI_ERR_NOMEM, "pairs buffer too small: " + std::to_string(total) + " pairs survive the filter");
+    uint64_t at = 0;
+    for (const auto& v : sv) {
+        if (!v.empty()) memcpy(pairs + at, v.data(), sizeof(lzani_pair_t) * v.size());
+        at += v.size();
+    }
+    return LZANI_OK;
+}
+
+}  // namespace
+
 extern "C" int lzani_run(lzani_ctx* c, uint32_t n_refs, const uint64_t* row_off, const uint32_t* q_ids,
                          lzani_result_t* out)
 {
     if (!c) return LZANI_ERR_ARG;
+    if (!c->subs.empty()) {
+        if (n_refs != c->n_seqs) return fail(c, LZANI_ERR_ARG, "n_refs must equal the number of sequences");
+        return group_run_rows(c, n_refs, nullptr, row_off, q_ids, 1, out, true);
+    }
     if (c->d_recs && n_refs != c->n_seqs) return fail(c, LZANI_ERR_ARG, "n_refs must equal the number of sequences");
     return run_rows_impl(c, n_refs, nullptr, row_off, q_ids, 1, out, true);
 }
@@ -787,6 +1017,7 @@ extern "C" int lzani_run(lzani_ctx* c, uint32_t n_refs, const uint64_t* row_off,
 extern "C" int lzani_run_rows(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const uint64_t* row_off,
                               const uint32_t* q_ids, lzani_result_t* out)
 {
+    if (c && !c->subs.empty()) return group_run_rows(c, n_rows, ref_ids, row_off, q_ids, 1, out, true);
     return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, 1, out, true);
 }
 
@@ -795,6 +1026,7 @@ extern "C" int lzani_run_rows_regions(lzani_ctx* c, uint32_t n_rows, const uint3
                                       lzani_region_t* regions, uint64_t regions_cap, uint64_t* n_regions)
 {
     const RegionReq rq{region_off, regions, regions_cap, n_regions};
+    if (c && !c->subs.empty()) return group_run_rows(c, n_rows, ref_ids, row_off, q_ids, 1, out, true, &rq);
     return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, 1, out, true, &rq);
 }
 
@@ -802,6 +1034,7 @@ extern "C" int lzani_run_rows_resident(lzani_ctx* c, uint32_t n_rows, const uint
                                        const uint64_t* row_off, const uint32_t* q_ids, int repeat,
                                        lzani_result_t* out)
 {
+    if (c && !c->subs.empty()) return group_run_rows(c, n_rows, ref_ids, row_off, q_ids, repeat, out, out != nullptr);
     return run_rows_impl(c, n_rows, ref_ids, row_off, q_ids, repeat, out, false);
 }
 
@@ -812,6 +1045,7 @@ extern "C" int lzani_filter_pairs(lzani_ctx* c, lzani_ctx* const* group, int n_g
 {
     static_assert(sizeof(lzani_pair_t) == sizeof(PairOut), "lzani_pair_t layout");
     if (!c) return LZANI_ERR_ARG;
+    if (!c->subs.empty()) return group_filter_pairs(c, eff_len, flt, pairs, cap, n_out);       // the group is its own `group`
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
     if (!eff_len || !flt || !n_out || (cap && !pairs)) return fail(c, LZANI_ERR_ARG, "eff_len / flt / pairs / n_out == NULL");
     if (!c->last_valid) return fail(c, LZANI_ERR_STATE, "no results on the device: run lzani_run_rows* first");
@@ -892,6 +1126,12 @@ extern "C" int lzani_build_pair_list(lzani_ctx* c, uint32_t n, uint64_t n_edges,
                                      uint32_t* q_ids, uint64_t cap, uint64_t* n_entries)
 {
     if (!c) return LZANI_ERR_ARG;
+    if (!c->subs.empty()) {          // any one device does: the list is host data again afterwards
+        const int rc = lzani_build_pair_list(c->subs[0], n, n_edges, edge_i, edge_j, reorder_map, row_off, q_ids, cap, n_entries);
+        if (rc != LZANI_OK) c->err = c->subs[0]->err;
+        c->timing.pairlist_ms = c->subs[0]->timing.pairlist_ms;
+        return rc;
+    }
     if (c->device < 0) return fail(c, LZANI_ERR_CUDA, "context has no device (lzani_create failed)");
     if (!row_off || !n_entries || (n_edges && (!edge_i || !edge_j))) return fail(c, LZANI_ERR_ARG, "edge / row_off / n_entries == NULL");
     const uint64_t n_keys = 2 * n_edges;

@@ -314,6 +314,9 @@ k_scan_matrix(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta, co
 }
 
 // input of the second scan: hit runs per word
+struct RunCount64 {
+    __host__ __device__ __forceinline__ unsigned long long operator()(uint32_t m) const { return (unsigned long long)__builtin_popcount(run_first_bits(m)); }
+};
 struct RunCount {
     __host__ __device__ __forceinline__ uint32_t operator()(uint32_t m) const { return (uint32_t)__builtin_popcount(run_first_bits(m)); }
 };
@@ -367,6 +370,19 @@ k_hit_probe(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, con
 // thread i takes the i-th longest job, then the i-th shortest.  The lanes of a warp then run about the same
 // number of rows in each pass, and every warp of the block about the same number in total.
 constexpr int LZ_SPEC_JOBS = 2 * LZ_SPEC_THREADS;
+// hit records are read AND written by the threads of k_hit_spec (each thread its own record; verified_link also reads a
+// successor's record, of which it uses only bits no k_hit_spec thread changes -- static_assert below): coherent loads
+// (ld.global.cg), never the read-only path
+__device__ __forceinline__ Rec ld_rec_cg(const Rec* p)
+{
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
+    Rec r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+    return r;
+}
+// what hit_spec_finish() may change: x[29,32) (link), z[25,32) (seed offset), w[18,32) (scan length, first seed);
+// what verified_link() reads of the successor: x[0,29), y, z flags [18,22), w[12,18)
+static_assert(HIT_ENTRY_RUN_SHIFT == 29 && HIT_X_SHIFT == 25 && HIT_X_SHIFT > 21, "spec fields overlap what verified_link reads of a successor");
+
 template <class PT>
 __global__ void __launch_bounds__(LZ_SPEC_THREADS)
 k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const HitEntry* __restrict__ list,
@@ -388,7 +404,7 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
         const uint32_t t = base + slot;
         key[h] = 63; rank[h] = 0;
         if (t < total) {
-            const Rec rec = ld_rec(hit_recs + t);
+            const Rec rec = ld_rec_cg(hit_recs + t);
             const PairDesc d = desc[list[t].pair];
             const SpecJob j = hit_spec_job(P, d.Dq - P.msl, list, (uint64_t)t, (uint64_t)total, rec);
             if (j.need) {
@@ -428,14 +444,14 @@ k_hit_spec(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, cons
         pv.q = it.q; pv.r = it.r;
         const int ks = spec_first_seed(pv, P, it.si0, it.sP0, it.K, P.mrd);
         const uint32_t to = base + o;
-        Rec r2 = ld_rec(hit_recs + to);
+        Rec r2 = ld_rec_cg(hit_recs + to);
         SpecJob jj; jj.si0 = it.si0; jj.sP0 = it.sP0; jj.K = it.K; jj.succ = it.succ; jj.need = true;
         hit_spec_finish(r2, jj, ks);
         // successor link (verified_link): needs this record complete and, of the successor, only what
         // k_hit_probe wrote (position, anchor, flags, backward extension) -- bits no k_hit_spec thread changes,
         // so it does not matter whether the successor's own scan has been folded in yet
         const uint32_t d = r2.x >> HIT_ENTRY_RUN_SHIFT;
-        if (d && verified_link(P, r2, ld_rec(hit_recs + to + d)) != d) r2.x &= (uint32_t)(LZ_STAGED_MAX_POS - 1);
+        if (d && verified_link(P, r2, ld_rec_cg(hit_recs + to + d)) != d) r2.x &= (uint32_t)(LZ_STAGED_MAX_POS - 1);
         reinterpret_cast<uint4*>(hit_recs)[to] = make_uint4(r2.x, r2.y, r2.z, r2.w);
     }
 }
@@ -796,7 +812,11 @@ size_t staged_scan_bytes(uint64_t n_items)
     cub::DeviceScan::ExclusiveSum(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n_items);
     auto it = thrust::make_transform_iterator((const uint32_t*)nullptr, RunCount{});
     cub::DeviceScan::ExclusiveSum(nullptr, b, it, (uint32_t*)nullptr, (int64_t)n_items);
-    return a > b ? a : b;
+    size_t r = 0;
+    auto it64 = thrust::make_transform_iterator((const uint32_t*)nullptr, RunCount64{});
+    cub::DeviceReduce::Sum(nullptr, r, it64, (unsigned long long*)nullptr, (int64_t)n_items);
+    a = a > b ? a : b;
+    return a > r ? a : r;
 }
 
 cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* recs, const SeqMeta* meta,
@@ -846,6 +866,13 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
     auto it = thrust::make_transform_iterator((const uint32_t*)B.hm, RunCount{});
     tb = B.tmp_bytes;
     return cub::DeviceScan::ExclusiveSum(B.tmp, tb, it, B.rec_off, (int64_t)n_words + 1, st);
+}
+
+cudaError_t launch_run_total(cudaStream_t st, const StagedBufs& B, uint64_t n_words)
+{
+    auto it = thrust::make_transform_iterator((const uint32_t*)B.hm, RunCount64{});
+    size_t tb = B.tmp_bytes;
+    return cub::DeviceReduce::Sum(B.tmp, tb, it, B.counter + 3, (int64_t)n_words, st);
 }
 
 cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,

@@ -102,7 +102,7 @@ struct StagedBufs {
     HitEntry* list;               // [records]
     Rec* recs;                    // [records]
     void* tmp; size_t tmp_bytes;  // CUB scan scratch
-    unsigned long long* counter;  // [3] work counters of the walk kernels
+    unsigned long long* counter;  // [4] work counters of the walk kernels; [3]: 64-bit hit-run total
     uint32_t* hard;               // [pairs] pairs the lane walk hands to the warp walk
 };
 // all2all form of the scan (k_bitmap_matrix + k_scan_matrix): the chunk is made of whole dense rows
@@ -122,6 +122,8 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
                                uint32_t n_rows, const uint32_t* q_ids, uint64_t pair_begin, uint32_t n_pairs,
                                uint64_t n_words, const Prm& P, const uint32_t* bitmap_pool, int scan_blocks,
                                const MatrixScan* mx = nullptr);
+// exact 64-bit number of hit runs of the chunk -> counter[3] (chunks whose 32-bit scan total could wrap)
+cudaError_t launch_run_total(cudaStream_t st, const StagedBufs& B, uint64_t n_words);
 // S2, S3, S4
 cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBufs& B, const Rec* recs,
                                uint64_t pair_begin, uint32_t n_pairs, uint64_t n_words, uint64_t n_recs, const Prm& P,

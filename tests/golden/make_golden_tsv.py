@@ -31,12 +31,33 @@ CASES = {
                           ["--out-filter", "tani", "0.85", "--out-filter", "rcov", "0.9", "--out-filter", "gani", "0.8"], None),
     "example_filter09_outfilter": (["--in-fasta", "example/multifasta.fna"],
                                    ["--flt-kmerdb", "example/fltr.txt", "0.9", "--out-filter", "ani", "0.97"], None),
+    # submits without pairs: a kmer-db filter nothing passes, a set of one sequence -- header-only output
+    "example_filter_none": (["--in-fasta", "example/multifasta.fna"], ["--flt-kmerdb", "example/fltr.txt", "1.5"], None),
+    "single_default": (["--in-fasta", "@first:example/multifasta.fna"], [], None),
 }
+
+
+def first_record(path, tmp):
+    """A FASTA holding only the first record of `path`."""
+    out = os.path.join(tmp, "first.fna")
+    with open(path) as f, open(out, "w") as o:
+        n = 0
+        for line in f:
+            if line.startswith(">"):
+                n += 1
+                if n > 1:
+                    break
+            o.write(line)
+    return out
 
 
 def main():
     tmp = tempfile.mkdtemp()
+    only = set(sys.argv[1:])
     for name, (inp, extra, fixture) in CASES.items():
+        if only and name not in only:
+            continue
+        inp = [first_record(os.path.join(REF, a[7:]), tmp) if a.startswith("@first:") else a for a in inp]
         out = os.path.join(tmp, name + ".tsv")
         args = [a if not (a.startswith("test/") or a.startswith("example/")) else os.path.join(REF, a) for a in inp + extra]
         subprocess.run([CLI, "all2all"] + args + ["--out", out, "-V", "1"], check=True, stderr=subprocess.DEVNULL)
@@ -50,6 +71,9 @@ def main():
         with gzip.GzipFile(os.path.join(HERE, name + ".ani.ids.tsv.gz"), "wb", mtime=0) as f:
             f.write(ids)
         print(name, len(data), hashlib.md5(data).hexdigest())
+    if only:
+        shutil.rmtree(tmp)
+        return
     # --out-alignment (line order depends on thread interleaving in the reference: compare sorted)
     out = os.path.join(tmp, "aln_main.tsv")
     aln = os.path.join(tmp, "aln.tsv")

@@ -209,6 +209,8 @@ def test_region_records_match_oracle(sname, params):
     dict(LZANI_STAGED_WORDS="300", LZANI_STAGED_RECS="40"),          # records overflow: chunks halved, single pairs grow the buffers
     dict(LZANI_STAGED_WORDS="20000", LZANI_MATRIX_SCAN="0"),         # probe scan with the folded bitmap in shared memory
     dict(LZANI_STAGED="0"),                                          # one-kernel form
+    dict(LZANI_LANE_WALK="0"),                                       # warp-per-pair walk for every pair (the lane walk hands it only the related ones)
+    dict(LZANI_LANE_WALK="0", LZANI_STAGED_WORDS="300"),
 ])
 def test_staged_chunking_paths(env, monkeypatch):
     """The host side of the staged parse under hostile capacities: chunk boundaries inside rows, record
@@ -239,3 +241,91 @@ def test_staged_chunking_paths(env, monkeypatch):
     full = GOLD["example_default"].reshape(n, n - 1, 3)
     want = np.array([full[r, x if x < r else x - 1] for r in range(n) for x in range(n) if x != r and (x + r) % 3 == 0])
     assert np.array_equal(got, want), env
+
+
+def _two_devices():
+    """Two device ids for the group tests: two GPUs when the box has them (peer access over NVLink), else the
+    same GPU twice (two device contexts sharing it: same host logic)."""
+    import torch
+    return [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
+
+
+def test_group_context_owns_the_devices():
+    """lzani_create(..., device_ids, n_devices > 1) -- ONE context, the library deals the reference rows
+    over its devices (dense: r mod G; sparse: heaviest rows first), runs them from its own worker threads and
+    hands back results in the caller's CSR order: dense all2all, sparse CSR with empty rows, row subsets, region
+    records and the device-side out-filter (each device reads the other's rows in place) must equal the
+    one-device answers."""
+    ss = mg.get_set("example")
+    n = len(ss)
+    dense = GOLD["example_default"]
+    single = lz.Matcher(device=0)
+    grp = lz.Matcher(devices=_two_devices())
+    try:
+        single.set_sequences(ss)
+        grp.set_sequences(ss)
+        assert np.array_equal(grp.all2all(), dense)
+        t = grp.timing()
+        assert t["n_pairs"] == n * (n - 1) and t["launches"] > 0
+        rng = np.random.default_rng(7)
+        off, q = [0], []
+        for r in range(n):
+            cnt = int(rng.integers(0, 5))
+            ids = rng.choice([x for x in range(n) if x != r], size=cnt, replace=False)
+            q.extend(sorted(int(x) for x in ids))
+            off.append(len(q))
+        off, q = np.array(off, np.uint64), np.array(q, np.uint32)
+        assert np.array_equal(grp.run(off, q), single.run(off, q))
+        rows = np.array([5, 0, 9, 3, 7], dtype=np.uint32)
+        assert np.array_equal(grp.run_rows(rows), single.run_rows(rows))
+        # empty submit: legal, returns nothing
+        assert grp.run_rows(np.zeros(0, np.uint32)).shape == (0, 3)
+        assert single.run_rows(np.zeros(0, np.uint32)).shape == (0, 3)
+        # regions
+        a = single.run_rows_regions(np.arange(n, dtype=np.uint32))
+        b = grp.run_rows_regions(np.arange(n, dtype=np.uint32), cap=8)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        # out-filter over results resident on both devices
+        eff = ss.lens.astype(np.uint32)
+        flt = dict(ani=0.9, qcov=0.3)
+        out = np.zeros((n * (n - 1), 3), dtype=np.int32)
+        single.run_rows(np.arange(n, dtype=np.uint32), out=out, resident_repeat=1)
+        want = single.filter_pairs(eff, flt)
+        grp.run_rows(np.arange(n, dtype=np.uint32), out=out, resident_repeat=1)
+        got = grp.filter_pairs(eff, flt)
+        key = lambda p: (int(p["a"]), int(p["b"]))
+        assert sorted(map(key, got)) == sorted(map(key, want)) and len(got) > 0
+        gd = {key(p): p for p in got}
+        for p in want:
+            g = gd[key(p)]
+            assert g["ab"].tolist() == p["ab"].tolist() and g["ba"].tolist() == p["ba"].tolist() and g["lines"] == p["lines"]
+    finally:
+        single.close()
+        grp.close()
+
+
+def test_more_than_65535_sequences_dense_rows():
+    """n > 65 535 sequences: the all2all matrix scan is off by construction (its grid's y dimension is the query
+    id), dense rows go through the probe scan.  Tiny sequences, a few reference rows, against the oracle."""
+    rng = np.random.default_rng(65)
+    n = 66_000
+    base = rng.integers(0, 4, size=90, dtype=np.uint8)
+    seqs = []
+    for i in range(n):
+        s = base.copy() if i % 7 == 0 else rng.integers(0, 4, size=int(rng.integers(40, 120)), dtype=np.uint8)
+        if i % 7 == 0:
+            s[rng.integers(0, 90, size=3)] = rng.integers(0, 4, size=3, dtype=np.uint8)
+        seqs.append(s)
+    ss = hostio.SeqSet([f"s{i}" for i in range(n)], seqs)
+    rows = np.array([0, 7, 65_999], dtype=np.uint32)
+    m = lz.Matcher(device=0)
+    try:
+        m.set_sequences(ss)
+        got = m.run_rows(rows)
+    finally:
+        m.close()
+    want = Oracle().run_rows(ss, None, rows=rows)
+    assert got.shape == (3 * (n - 1), 3)
+    assert np.array_equal(got, want)
+    assert int(got[:, 2].sum()) > 1000          # the near-copies of `base` do align

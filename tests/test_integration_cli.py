@@ -70,6 +70,14 @@ def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
     ("vir61_outfilter", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
     ("example_outfilter", "example", ["--out-filter", "tani", "0.85", "--out-filter", "rcov", "0.9", "--out-filter", "gani", "0.8"]),
     ("example_filter09_outfilter", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
+    # submits without pairs: a filter nothing passes, a set of one sequence -- header-only output like the reference's
+    ("example_filter_none", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "1.5"]),
+    ("example_filter_none@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "1.5", "--out-filter", "ani", "0.5"]),
+    ("single_default", "example", []),
+    ("single_default@2ctx", "example", []),
+    # one library context driving two device contexts (lzani_create with n_devices = 2): rows dealt by the library
+    ("vir61_default@2ctx", "vir61", []),
+    ("example_filter09@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9"]),
     # the same with the rows dealt over two contexts that read each other's results in place
     ("vir61_outfilter@2ctx", "vir61", ["--out-filter", "ani", "0.9", "--out-filter", "qcov", "0.3"]),
     ("example_filter09_outfilter@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
@@ -97,6 +105,8 @@ def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
         hdr = open(os.path.join(GOLD, "example_fltr.txt")).readline().rstrip("\n").split(",")[1:]
         hdr = [h for h in hdr if h]
         order = [ss.names.index(h) for h in hdr]
+    if case.startswith("single_"):
+        order = [ss.names.index("NC_010807.ref")]      # the first record of example/multifasta.fna
     fa = tmp_path / "in.fna"
     write_fasta(fa, ss, order)
     out = tmp_path / "ani.tsv"
@@ -109,17 +119,19 @@ def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
 
 
 @pytest.mark.gpu
-def test_cli_out_alignment_identical_to_reference(tmp_path):
+@pytest.mark.parametrize("devices", ["0", "0,0"])
+def test_cli_out_alignment_identical_to_reference(tmp_path, devices):
     """--out-alignment: region records from the B200 regions kernel written by the reference's own
     store_alignment; the reference's line order depends on thread interleaving, so sorted lines are
-    compared."""
+    compared.  "0,0": the library's group path (region lists of two device contexts stitched
+    back into CSR order)."""
     need_cli()
     ss = mg.get_set("example")
     fa = tmp_path / "in.fna"
     write_fasta(fa, ss)
     out, aln = tmp_path / "ani.tsv", tmp_path / "ani.aln.tsv"
     r = subprocess.run([CLI, "all2all", "--in-fasta", str(fa), "--out", str(out), "--out-alignment", str(aln), "-V", "1"],
-                       capture_output=True, text=True)
+                       capture_output=True, text=True, env=dict(os.environ, LZANI_DEVICES=devices))
     assert r.returncode == 0, r.stderr
     want = gzip.open(os.path.join(GOLD, "example_default.aln.sorted.tsv.gz")).read().splitlines(keepends=True)
     got = sorted(open(aln, "rb").read().splitlines(keepends=True))
