@@ -24,6 +24,7 @@
 // error and exits 1 (the reference's own error convention, lz_matcher.h:61-65).
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <iostream>
 #include <string>
@@ -109,9 +110,21 @@ void CLZMatcher::do_matching()
     const uint32_t G = (uint32_t)devs.size();
     const unsigned host_threads = std::max(1u, params.no_threads ? (unsigned)params.no_threads : std::thread::hardware_concurrency());
 
+    // where the matching stage goes (-V 2): context creation, sequence upload, device submits, building the result rows
+    using clk = std::chrono::steady_clock;
+    auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+    double t_submit = 0, t_rows = 0;
+    const auto t_begin = clk::now();
     lzani_ctx* ctx = nullptr;
     if (lzani_create(&ctx, &P, devs.data(), (int)G) != LZANI_OK) die("lzani_create", ctx);
+    const auto t_created = clk::now();
     if (lzani_set_sequences(ctx, n, data.data(), len.data()) != LZANI_OK) die("lzani_set_sequences", ctx);
+    const auto t_loaded = clk::now();
+    auto report = [&] {
+        if (params.verbosity_level >= 2)
+            cerr << "  B200 matching stage: create " << secs(t_begin, t_created) << " s, sequences to " << G << " GPU(s) " << secs(t_created, t_loaded)
+                 << " s, submits " << t_submit << " s, result rows " << t_rows << " s" << endl;
+    };
 
     // the pair list in CSR form (sparse lists: the filter's rows, ids ascending)
     uint64_t total_pairs = 0;
@@ -148,6 +161,7 @@ void CLZMatcher::do_matching()
             }
         }
         // one submit with every row; the results stay on the GPUs that parsed them
+        const auto t_s0 = clk::now();
         if (lzani_run_rows_resident(ctx, n, nullptr, dense ? nullptr : row_off.data(), dense ? nullptr : q_ids.data(), 1, nullptr) != LZANI_OK)
             die("lzani_run_rows_resident", ctx);
         std::vector<lzani_pair_t> sv(1024);
@@ -159,6 +173,8 @@ void CLZMatcher::do_matching()
             sv.resize(need);
             break;
         }
+        const auto t_s1 = clk::now();
+        t_submit = secs(t_s0, t_s1);
         // only the surviving pairs reach the host: both directions go into `results`, id-sorted, as
         // store_results expects them (lz_matcher.cpp:404-418)
         for (const lzani_pair_t& p : sv) {
@@ -166,8 +182,10 @@ void CLZMatcher::do_matching()
             results[p.b].emplace_back(p.a, results_t(p.ba.sym_in_matches, p.ba.sym_in_literals, p.ba.no_components));
         }
         parallel_rows(n, host_threads, [&](size_t r) { std::sort(results[r].begin(), results[r].end()); });
+        t_rows = secs(t_s1, clk::now());
         lzani_destroy(ctx);
         if (params.verbosity_level >= 2) cerr << endl;
+        report();
         return;
     }
 
@@ -197,6 +215,7 @@ void CLZMatcher::do_matching()
             ++r;
         }
         out.resize(pairs);
+        const auto t_s0 = clk::now();
         if (pairs) {        // (a set of one sequence, or a filter nothing passes: nothing to submit, header-only output)
             if (f_alignment) {
                 region_off.resize(pairs + 1);
@@ -216,6 +235,8 @@ void CLZMatcher::do_matching()
                 if (rc != LZANI_OK) die("lzani_run_rows", ctx);
             }
         }
+        const auto t_s1 = clk::now();
+        t_submit += secs(t_s0, t_s1);
         auto fill_row = [&](size_t j) {
             const uint32_t ref = rows[j];
             vec_id_results_t res_row;
@@ -248,10 +269,12 @@ void CLZMatcher::do_matching()
                 }
         }
         if (!dense) for (uint32_t ref : rows) filter.clear_row(ref);
+        t_rows += secs(t_s1, clk::now());
         if (params.verbosity_level >= 2)
             cerr << "Sequences: " + std::to_string(100ull * r / (n ? n : 1)) + "%       \r" << std::flush;
     }
     lzani_destroy(ctx);
     if (params.verbosity_level >= 2)
         cerr << endl;
+    report();
 }

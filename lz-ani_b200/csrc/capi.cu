@@ -202,11 +202,20 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     if (n_devices > 1) {
         if (!device_ids) return fail(c, LZANI_ERR_ARG, "device_ids == NULL with n_devices > 1");
         // (a device may be named twice: two contexts sharing one GPU -- how the group path is tested on a one-GPU box)
-        for (int g = 0; g < n_devices; ++g) {
-            lzani_ctx* sub = nullptr;
-            const int rc = lzani_create(&sub, p, device_ids + g, 1);
-            if (sub) c->subs.push_back(sub);
-            if (rc != LZANI_OK) return fail(c, rc, "device " + std::to_string(device_ids[g]) + ": " + (sub ? sub->err : std::string("allocation failed")));
+        // one thread per device: CUDA context creation (~1 s per GPU) runs side by side
+        c->subs.assign((size_t)n_devices, nullptr);
+        std::vector<int> rcs((size_t)n_devices, LZANI_OK);
+        std::vector<std::thread> th;
+        for (int g = 0; g < n_devices; ++g) th.emplace_back([&, g] { rcs[g] = lzani_create(&c->subs[g], p, device_ids + g, 1); });
+        for (auto& t : th) t.join();
+        int bad = -1;
+        for (int g = 0; g < n_devices; ++g) if (rcs[g] != LZANI_OK && bad < 0) bad = g;
+        if (bad >= 0) {
+            const int rc = rcs[bad];
+            const std::string msg = "device " + std::to_string(device_ids[bad]) + ": " + (c->subs[bad] ? c->subs[bad]->err : std::string("allocation failed"));
+            for (lzani_ctx*& sub : c->subs) { if (sub) lzani_destroy(sub); sub = nullptr; }
+            c->subs.clear();
+            return fail(c, rc, msg);
         }
         return LZANI_OK;
     }

@@ -26,11 +26,11 @@ PY
 T=$(nproc)
 run() { # name, args...
   local name=$1; shift
-  local t0=$(date +%s.%N)
+  local t0=$(date +%s%N)
   "$@" 2> $D/$name.err > /dev/null
-  local t1=$(date +%s.%N)
-  echo "== $name: wall $(echo "$t1 - $t0" | bc) s"
-  grep -E "time|Time|matching|Loading|Stor|Reorder|Total" $D/$name.err | tr '\r' '\n' | grep -v "^Sequences" | tail -12
+  local t1=$(date +%s%N)
+  echo "== $name: wall $(( (t1 - t0) / 1000000 )) ms"
+  grep -E "time|Time|matching|Loading|Stor|Reorder|Total|B200" $D/$name.err | tr '\r' '\n' | grep -v "^Sequences" | tail -12
 }
 export LZANI_DEVICES=$DEV
 run "b200_plain_dev$DEV" integration/_build/lz-ani-b200 all2all --in-fasta $D/set.fna --out $D/o1.tsv -V 2 -t $T
