@@ -34,6 +34,8 @@
 #include "lz_matcher.h"          // reference header (-I /root/reference/src)
 #include "lzani_b200.h"          // our C ABI (-I include)
 
+bool lzani_device_ingest();      // loader_hooks_b200.cpp
+
 namespace {
 
 std::vector<int> devices_from_env()
@@ -118,7 +120,10 @@ void CLZMatcher::do_matching()
     lzani_ctx* ctx = nullptr;
     if (lzani_create(&ctx, &P, devs.data(), (int)G) != LZANI_OK) die("lzani_create", ctx);
     const auto t_created = clk::now();
-    if (lzani_set_sequences(ctx, n, data.data(), len.data()) != LZANI_OK) die("lzani_set_sequences", ctx);
+    if (lzani_device_ingest()) {
+        // LZANI_DEVICE_INGEST=1: the reservoir holds the loader's text (loader_hooks_b200.cpp); packing happens on the device
+        if (lzani_set_sequences_text(ctx, n, data.data(), len.data()) != LZANI_OK) die("lzani_set_sequences_text", ctx);
+    } else if (lzani_set_sequences(ctx, n, data.data(), len.data()) != LZANI_OK) die("lzani_set_sequences", ctx);
     const auto t_loaded = clk::now();
     auto report = [&] {
         if (params.verbosity_level >= 2)

@@ -75,6 +75,12 @@ def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
     ("example_filter_none@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "1.5", "--out-filter", "ani", "0.5"]),
     ("single_default", "example", []),
     ("single_default@2ctx", "example", []),
+    # SURVEY 8f-3 / 8f-4 from the product binary: the reservoir keeps the loader's text and K1 packs on the device
+    # (LZANI_DEVICE_INGEST); the filter's id remap + row sort + CSR are built on the device (LZANI_DEVICE_PAIRLIST)
+    ("vir61_default@ingest", "vir61", []),
+    ("example_default@ingest", "example", []),
+    ("example_filter09@pairlist", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9"]),
+    ("example_filter09_outfilter@pairlist+ingest", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9", "--out-filter", "ani", "0.97"]),
     # one library context driving two device contexts (lzani_create with n_devices = 2): rows dealt by the library
     ("vir61_default@2ctx", "vir61", []),
     ("example_filter09@2ctx", "example", ["--flt-kmerdb", os.path.join(GOLD, "example_fltr.txt"), "0.9"]),
@@ -89,6 +95,12 @@ def test_cli_has_no_cpu_path_and_fails_loudly_without_gpu(tmp_path):
 def test_cli_tsv_byte_identical_to_reference(tmp_path, case, setname, extra):
     need_cli()
     env = dict(os.environ)
+    if "@" in case and case.split("@")[1] in ("ingest", "pairlist", "pairlist+ingest"):
+        case, sw = case.split("@")
+        if "ingest" in sw:
+            env["LZANI_DEVICE_INGEST"] = "1"
+        if "pairlist" in sw:
+            env["LZANI_DEVICE_PAIRLIST"] = "1"
     if case.endswith("@2ctx"):
         case = case[:-5]
         env["LZANI_DEVICES"] = "0,0"
