@@ -24,7 +24,7 @@ def main():
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hi]
     col = {h: i for i, h in enumerate(hdr)}
-    data = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+    data = [r for r in rows[hi + 1:] if len(r) == len(hdr) and r[0].startswith("0x")]
     sl = n.sass_lines(sass, func_sub)
     base = int(data[0][0], 16)
     by_off = {o: (t, l) for o, t, l in sl}
