@@ -547,9 +547,22 @@ k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
                     if (k < n_pairs) {
                         const uint32_t pl = (uint32_t)k;
                         const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
+                        const PairDesc pd = desc[pl];
+                        // Related genomes show in the hit records before any walking: an unrelated pair has about
+                        // 32 * rho * (1 - rho) hit runs per 32 query positions, rho = the share of all mal-mers the reference
+                        // holds.  A pair with LZ_LANE_DENSE_PCT % of that or more would only park its way to the hand-over:
+                        // it goes to the warp-per-pair walk at once.
+                        const uint32_t nw = word_off[pl + 1] - word_off[pl];
+                        const float rho = fminf(1.0f, (float)pd.Dr * exp2f(-2.0f * (float)P.mal));
+                        if ((float)(r1 - r0) * 100.0f > (float)LZ_LANE_DENSE_PCT * 32.0f * rho * (1.0f - rho) * (float)nw + 6400.0f) {
+                            hard_list[atomicAdd(hard_count, 1ull)] = pl;
+                            mode[j] = LANE_DONE;        // the slot takes another pair next round
+                            live = true;
+                            continue;
+                        }
                         LaneCtx L;
                         PairView pv{};
-                        pv.Dq = desc[pl].Dq;
+                        pv.Dq = pd.Dq;
                         lane_begin(L, pv, hit_recs + r0, r1 - r0, P.msl);
                         lane_ctx_store(slots, j, L, r0, pl, 0);
                         mode[j] = LANE_RUN;

@@ -45,6 +45,10 @@
 #endif
 // a lane hands its pair to the warp-per-pair walk after BASE + (query positions >> SHIFT) parked steps (an unrelated
 // 50 kb pair parks ~120 times, a related one 600-1300 times)
+// ... and a pair whose hit runs number this many percent of what an unrelated pair would show goes there at once
+#ifndef LZ_LANE_DENSE_PCT
+#define LZ_LANE_DENSE_PCT 125
+#endif
 #ifndef LZ_LANE_HARD_BASE
 #define LZ_LANE_HARD_BASE 64
 #endif
