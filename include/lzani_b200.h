@@ -26,6 +26,7 @@
 #ifndef LZANI_B200_H
 #define LZANI_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -189,6 +190,34 @@ int lzani_filter_pairs(lzani_ctx* ctx, lzani_ctx* const* group, int n_group, con
 int lzani_build_pair_list(lzani_ctx* ctx, uint32_t n, uint64_t n_edges, const uint32_t* edge_i,
                           const uint32_t* edge_j, const uint32_t* reorder_map, uint64_t* row_off,
                           uint32_t* q_ids, uint64_t cap, uint64_t* n_entries);
+
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The --out-filter pre-filter of lzani_filter_pairs() over a DENSE all2all result matrix the
+ * caller already holds in device memory, allocating nothing: the kernels' scratch (a flag byte per
+ * ordered pair, a count and an offset per 256 pairs) is one file-scope __device__ array of about
+ * 4.2 MB, sized for LZANI_NOALLOC_MAX_SEQS sequences, that every GPU which loads the library holds
+ * until the process exits.  The call makes no cudaMalloc / cudaFree / allocating library call and
+ * does not synchronise: it launches three kernels on `stream` (a cudaStream_t, NULL = the default
+ * stream) of `device` and returns.  (The first call per device looks the array's address up with
+ * cudaGetSymbolAddress; make that first call outside a graph capture.)
+ *   d_res     DEVICE: n_seqs * (n_seqs - 1) results, row r = reference r, its queries = every id != r
+ *             ascending (what lzani_run / lzani_run_rows write for the dense pair list)
+ *   d_eff_len DEVICE: n_seqs lengths without contig separators (as lzani_filter_pairs' eff_len)
+ *   flt       HOST: the thresholds
+ *   d_pairs   DEVICE: room for `cap` surviving pairs, written in CSR order like lzani_filter_pairs
+ *   d_n_out   DEVICE: the number of surviving pairs -- the full count even when it exceeds cap (then
+ *             only the first cap are written); 2^64-1 if the scratch address check failed on the device
+ *   err       HOST, may be NULL: receives a message when the return value is not LZANI_OK
+ * n_seqs > LZANI_NOALLOC_MAX_SEQS is rejected with LZANI_ERR_ARG (use lzani_filter_pairs).  All calls
+ * on one device share the scratch array: calls that overlap on the GPU race -- keep them on one stream
+ * or order them yourself.  The array keeps the previous call's contents; every word a call reads it
+ * has written itself, so nothing needs clearing between calls. */
+#define LZANI_NOALLOC_MAX_SEQS 2048
+int lzani_filter_dense_noalloc(int device, uint32_t n_seqs, const lzani_result_t* d_res,
+                               const uint32_t* d_eff_len, const lzani_out_filter_t* flt,
+                               lzani_pair_t* d_pairs, uint64_t cap, uint64_t* d_n_out, void* stream,
+                               char* err, size_t err_len);
 
 int lzani_get_timing(const lzani_ctx* ctx, lzani_timing_t* t);
 

@@ -35,7 +35,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA extension in-tree for sm_100a (cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "pairlist.cu", "capi.cu")]
+    srcs = [os.path.join(CSRC, f) for f in ("kernels.cu", "postproc.cu", "pairlist.cu", "capi.cu", "noalloc.cu")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("kernels.h", "layout.h", "parse_core.h", "lane_walk.h", "regions.h", "simt.h", "outfilter.h")] + [
         os.path.join(ROOT, "include", "lzani_b200.h")]
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
@@ -84,6 +84,7 @@ def load_library() -> C.CDLL:
     lib.lzani_run_rows_regions.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, u64, vp]
     lib.lzani_filter_pairs.argtypes = [vp, vp, C.c_int, vp, vp, vp, u64, vp]
     lib.lzani_build_pair_list.argtypes = [vp, u32, u64, vp, vp, vp, vp, vp, u64, vp]
+    lib.lzani_filter_dense_noalloc.argtypes = [C.c_int, u32, vp, vp, vp, vp, u64, vp, vp, C.c_char_p, C.c_size_t]
     lib.lzani_get_timing.argtypes = [vp, C.POINTER(TimingStruct)]
     lib.lzani_set_index_budget.argtypes = [vp, u64]
     lib.lzani_last_error.argtypes = [vp]

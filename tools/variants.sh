@@ -8,7 +8,7 @@ S=lz-ani_b200/csrc
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   ( nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared $flags \
-      $S/kernels.cu $S/postproc.cu $S/pairlist.cu $S/capi.cu -o lz-ani_b200/variants/lib$name.so && echo "built $name" ) &
+      $S/kernels.cu $S/postproc.cu $S/pairlist.cu $S/capi.cu $S/noalloc.cu -o lz-ani_b200/variants/lib$name.so && echo "built $name" ) &
   # at most 3 compiles at a time
   while [ "$(jobs -rp | wc -l)" -ge 3 ]; do sleep 1; done
 done
