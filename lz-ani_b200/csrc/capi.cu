@@ -79,7 +79,8 @@ struct lzani_ctx {
         cudaStream_t st = nullptr;
         cudaEvent_t done = nullptr;
         uint32_t* h_total = nullptr;      // pinned: records of the chunk
-        uint32_t* mc = nullptr;           // all2all scan: k-mer x reference bit matrix (4^mal words)
+        uint32_t* mc = nullptr;           // all2all scan: bitmap-bit x reference matrix (2^bbits words)
+        uint64_t mc_words = 0;
     } slot[2];
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
@@ -740,13 +741,23 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     // all2all form of the scan when the chunk is made of whole dense rows and the bitmaps are direct
                     MatrixScan mx{};
                     bool use_mx = false;
-                    if (!q_ids && c->matrix_scan && 2 * P.mal <= 22 && n <= 65535u && np) {
+                    if (!q_ids && c->matrix_scan && P.mal <= 32 && n <= 65535u && np) {
                         const uint32_t ja = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k0) - row_off.begin()) - 1;
                         const uint32_t jb = (uint32_t)(std::upper_bound(row_off.begin(), row_off.end(), ch.k1 - 1) - row_off.begin());
-                        if (row_off[ja] == ch.k0 && row_off[jb] == ch.k1) {
-                            // 4^mal words, written 32 at a time (k_bitmap_matrix): never fewer than 32
-                            if (!sl.mc) LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) * std::max<uint64_t>(32, (uint64_t)1 << (2 * P.mal))));
-                            mx.mc = sl.mc; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
+                        // one bitmap size for every row of the chunk (direct bitmaps: always; hashed ones: references of
+                        // similar length), at most 2^30 bits = a 4 GB matrix
+                        uint32_t bb = plan[ja].bbits;
+                        for (uint32_t j = ja; j < jb; ++j) if (plan[j].bbits != bb) bb = 0;
+                        if (row_off[ja] == ch.k0 && row_off[jb] == ch.k1 && bb && bb <= 30u) {
+                            // 2^bbits words, written 32 at a time (k_bitmap_matrix): never fewer than 32
+                            const uint64_t mw = std::max<uint64_t>(32, (uint64_t)1 << bb);
+                            if (mw > sl.mc_words) {
+                                LZ_CUDA(c, cudaStreamSynchronize(sl.st));
+                                cudaFree(sl.mc); sl.mc = nullptr; sl.mc_words = 0;
+                                LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) * mw));
+                                sl.mc_words = mw;
+                            }
+                            mx.mc = sl.mc; mx.bbits = bb; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
                             use_mx = true;
                         }
                     }

@@ -269,7 +269,7 @@ template <class PT>
 __global__ void __launch_bounds__(128)
 k_scan_matrix(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta, const uint32_t* __restrict__ row_ref,
               const uint64_t* __restrict__ row_off, uint32_t nr, uint64_t chunk_k0,
-              const uint32_t* __restrict__ word_off, PT P, const uint32_t* __restrict__ mc, uint32_t key_mask,
+              const uint32_t* __restrict__ word_off, PT P, const uint32_t* __restrict__ mc, uint32_t key_mask, uint32_t bbits,
               uint32_t* __restrict__ hm, uint32_t* __restrict__ wpair)
 {
     __shared__ uint32_t s_ref[32];
@@ -293,12 +293,20 @@ k_scan_matrix(const Rec* __restrict__ recs, const SeqMeta* __restrict__ meta, co
     const Rec* qr = recs + mq.q_rec;
     const Rec a = ld_rec(qr + w), b = ld_rec(qr + w + 1);
     const uint32_t km = low_mask32(P.mal);
-    const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
     uint32_t v[32];
+    if (2 * P.mal <= LZ_DIRECT_BITMAP_MAX_BITS) {     // direct bitmaps: the matrix is indexed by the k-mer itself
+        const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
 #pragma unroll
-    for (int t = 0; t < 32; ++t) {
-        const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
-        v[t] = __ldg(mc + (((lo & km) | (hs & ~km)) & key_mask));
+        for (int t = 0; t < 32; ++t) {
+            const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
+            v[t] = __ldg(mc + (((lo & km) | (hs & ~km)) & key_mask));
+        }
+    } else {                                          // hashed bitmaps of one size: by the bitmaps' common bit index
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+            const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+            v[t] = __ldg(mc + bitmap_index(kmer_key(lo, hi, P.mal), P.mal, bbits));
+        }
     }
     transpose32(v);
     const uint32_t valid = scan_valid_mask(a, b, P.mal, (int)(32u * w), n_loop);
@@ -849,8 +857,8 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
     if (e != cudaSuccess) return e;
     if (n_words && mx) {
         // all2all form: blocks of <= 32 whole rows
-        const uint32_t key_words = ((1u << (2 * P.mal)) + 31u) / 32u;
-        const uint32_t key_mask = (1u << (2 * P.mal)) - 1u;
+        const uint32_t key_words = (uint32_t)((((uint64_t)1 << mx->bbits) + 31u) / 32u);
+        const uint32_t key_mask = (uint32_t)(((uint64_t)1 << mx->bbits) - 1u);
         for (uint32_t i0 = 0; i0 < mx->n_rows_chunk; i0 += 32) {
             const uint32_t nr = mx->n_rows_chunk - i0 < 32u ? mx->n_rows_chunk - i0 : 32u;
             k_bitmap_matrix<<<(key_words + 255) / 256, 256, 0, st>>>(bitmap_pool, row_idx + mx->row_first + i0, nr, key_words, mx->mc);
@@ -859,7 +867,7 @@ cudaError_t launch_staged_scan(cudaStream_t st, const StagedBufs& B, const Rec* 
             e = with_prm(P, [&](auto PT) {
                 const dim3 grid((mx->max_words + 127) / 128, mx->n_seqs);
                 k_scan_matrix<<<grid, 128, 0, st>>>(recs, meta, row_ref + mx->row_first + i0, row_off + mx->row_first + i0, nr,
-                                                    pair_begin, B.word_off, PT, mx->mc, key_mask, B.hm, B.wpair);
+                                                    pair_begin, B.word_off, PT, mx->mc, key_mask, mx->bbits, B.hm, B.wpair);
                 return cudaGetLastError();
             });
             if (e != cudaSuccess) return e;

@@ -111,7 +111,8 @@ struct StagedBufs {
 };
 // all2all form of the scan (k_bitmap_matrix + k_scan_matrix): the chunk is made of whole dense rows
 struct MatrixScan {
-    uint32_t* mc;                 // [4^mal] one word per k-mer: which of the block's <= 32 references have it
+    uint32_t* mc;                 // [2^bbits] one word per bitmap bit (direct bitmaps: per k-mer): which of the block's <= 32 references have it
+    uint32_t bbits;               // log2(bits) of every bitmap of the chunk's rows (they must agree)
     uint32_t row_first;           // first row of the chunk, relative to the row arrays handed to the launch
     uint32_t n_rows_chunk;
     uint32_t n_seqs;              // queries = every sequence

@@ -265,7 +265,7 @@ extern "C" int lzani_emul_matrix_scan_check(const int32_t* p8, const uint8_t* re
                                             uint32_t qry_len, int col, uint32_t noise)
 {
     Prm P{p8[0], p8[1], p8[2], p8[3], p8[4], p8[5], p8[6], p8[7]};
-    if (2 * P.mal > 22) return -1;
+    if (P.mal > 32) return -1;
     HostSeq r, q;
     build_seq(r, ref3, ref_len, P);
     build_seq(q, qry3, qry_len, P);
@@ -294,11 +294,18 @@ extern "C" int lzani_emul_matrix_scan_check(const int32_t* p8, const uint8_t* re
     int bad = 0;
     for (int wd = 0; wd < n_words; ++wd) {
         const Rec a = pv.q[wd], b = pv.q[wd + 1];
-        const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
         uint32_t v[32];
-        for (int t = 0; t < 32; ++t) {
-            const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
-            v[t] = mc[((lo & km) | (hs & ~km)) & kmask];
+        if (2 * P.mal <= LZ_DIRECT_BITMAP_MAX_BITS) {
+            const uint32_t h0 = a.y << P.mal, h1 = funnel_r(a.y, b.y, 32 - P.mal);
+            for (int t = 0; t < 32; ++t) {
+                const uint32_t lo = funnel_r(a.x, b.x, t), hs = funnel_r(h0, h1, t);
+                v[t] = mc[((lo & km) | (hs & ~km)) & kmask];
+            }
+        } else {                       // hashed bitmaps of one size
+            for (int t = 0; t < 32; ++t) {
+                const uint32_t lo = funnel_r(a.x, b.x, t), hi = funnel_r(a.y, b.y, t);
+                v[t] = mc[bitmap_index(kmer_key(lo, hi, P.mal), P.mal, ix.bbits)];
+            }
         }
         transpose32(v);
         const uint32_t m = v[col] & scan_valid_mask(a, b, P.mal, 32 * wd, n_loop);

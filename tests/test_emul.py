@@ -123,23 +123,30 @@ def test_transpose32_is_a_bit_matrix_transpose(emul):
 
 
 @pytest.mark.parametrize("params", [None, dict(mal=8, msl=4, mrd=7, mqd=3, reg=10, aw=4, am=1, ar=1),
-                                    dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1)])
-def test_matrix_scan_equals_probe_scan(emul, params):
+                                    dict(mal=2, msl=2, mrd=3, mqd=2, reg=4, aw=3, am=1, ar=1),
+                                    dict(mal=12, msl=7, mrd=40, mqd=40, reg=35, aw=15, am=7, ar=3),     # direct, 24 bits
+                                    mg.LONGP,                                                           # hashed bitmap, 30-bit keys
+                                    dict(mal=17, msl=10, mrd=33, mqd=90, reg=50, aw=32, am=12, ar=5),   # hashed, keys beyond 32 bits
+                                    dict(mal=32, msl=10, mrd=33, mqd=90, reg=50, aw=32, am=12, ar=5)])  # hashed, 64-bit keys
+def test_matrix_scan_equals_probe_scan(emul, params, request):
     """all2all form of the scan (bitmaps of 32 references transposed into one word per k-mer, one gather per
     query position, transpose back) against scan_word(), incl. N runs and the end of the loop."""
+    if "staged_lane" not in request.node.name:
+        pytest.skip("the scan is the same in every form of the walk: checked once")
     ss = mg.get_set("edge")
     names, seqs = synth.families(1, 3, 2000, 3000, seed=9)
     ss2 = hostio.SeqSet(names, seqs)
     p8 = hostio.params_array(params)
     checked = 0
+    big = params is not None and params["mal"] >= 12      # 2^24-bit bitmaps and up: a few pairs per set do
     for s_ in (ss, ss2):
         n = len(s_)
         for r in range(n):
             for q in range(n):
-                if r == q:
+                if r == q or (big and (r * n + q) % 5 != 1):
                     continue
                 bad = emul.lib.lzani_emul_matrix_scan_check(p8.ctypes.data, s_.packed[r].ctypes.data, int(s_.lens[r]),
                                                             s_.packed[q].ctypes.data, int(s_.lens[q]), (r * 7 + q) % 32, r * 131 + q)
                 assert bad == 0, (r, q, bad)
                 checked += 1
-    assert checked > 20
+    assert checked > (4 if big else 20)

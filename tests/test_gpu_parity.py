@@ -204,6 +204,30 @@ def test_region_records_match_oracle(sname, params):
         m.close()
 
 
+@pytest.mark.parametrize("params", [mg.LONGP, dict(mal=17, msl=10, mrd=33, mqd=90, reg=50, aw=32, am=12, ar=5),
+                                    dict(mal=12, msl=7, mrd=40, mqd=40, reg=35, aw=15, am=7, ar=3)])
+def test_matrix_scan_over_hashed_bitmaps(params, monkeypatch):
+    """Long anchors (2*mal > 24 bits): the bitmaps are hashed.  References of similar length get bitmaps of one size and
+    the all2all scan then serves 32 of them per gather, like the direct form; a chunk whose bitmaps differ in size
+    falls back to the probe scan.  Same integers either way, and as the oracle's."""
+    names, seqs = synth.families(3, 6, 6000, 6100, seed=41, block=(200, 900))       # Dr within one power of two
+    names2, seqs2 = synth.families(1, 4, 20000, 21000, seed=42)                     # a second bitmap size
+    names2 = ["long_" + x for x in names2]
+    hashed = 2 * params["mal"] > 24
+    for label, (nm, sq) in dict(uniform=(list(names), list(seqs)), mixed=(list(names) + names2, list(seqs) + list(seqs2))).items():
+        ss = hostio.SeqSet(nm, sq)
+        monkeypatch.setenv("LZANI_MATRIX_SCAN", "1")
+        got, t1 = run_gpu(ss, params)
+        monkeypatch.setenv("LZANI_MATRIX_SCAN", "0")
+        probe, t0 = run_gpu(ss, params)
+        assert np.array_equal(got, probe), label
+        assert np.array_equal(got, Oracle().run_rows(ss, params)), label
+        if label == "uniform" or not hashed:
+            assert t1["launches"] != t0["launches"], "the matrix form of the scan did not run"
+        else:
+            assert t1["launches"] == t0["launches"], "bitmaps of two sizes in one chunk must take the probe scan"
+
+
 @pytest.mark.parametrize("env", [
     dict(LZANI_STAGED_WORDS="300"),                                  # many chunks, rows cut in the middle (probe scan for those)
     dict(LZANI_STAGED_WORDS="300", LZANI_STAGED_RECS="40"),          # records overflow: chunks halved, single pairs grow the buffers
