@@ -804,6 +804,7 @@ template <class F>
 static cudaError_t with_prm(const Prm& P, F f)
 {
     if (is_default_kernel_params(P)) return f(PrmDefault{P.mrd, P.mqd, P.reg});
+    if (is_long_kernel_params(P)) return f(PrmLong{P.mrd, P.mqd, P.reg});
     return f(P);
 }
 
@@ -812,6 +813,8 @@ int walk_blocks_per_sm(const Prm& P)
     int nb = 0;
     const cudaError_t e = is_default_kernel_params(P)
         ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_pairs<PrmDefault>, LZ_WALK_THREADS, 0)
+        : is_long_kernel_params(P)
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_pairs<PrmLong>, LZ_WALK_THREADS, 0)
         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_walk_pairs<Prm>, LZ_WALK_THREADS, 0);
     if (e != cudaSuccess || nb < 1) nb = 1;
     return nb;
@@ -911,7 +914,7 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
                 recs, B.desc, B.list, B.rec_off + n_words, PT, bitmap_pool, table_pool, B.recs);
             cudaError_t e1 = cudaGetLastError();
             if (e1 != cudaSuccess) return e1;
-            if (decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K)
+            if constexpr (decltype(PT)::kSpecSeeds) if (PT.mqd <= SPEC_MAX_K)
                 k_hit_spec<<<(unsigned)((n_recs + LZ_SPEC_JOBS - 1) / LZ_SPEC_JOBS), LZ_SPEC_THREADS, 0, st>>>(
                     recs, B.desc, B.list, B.rec_off + n_words, PT, B.recs);
             return cudaGetLastError();
@@ -922,7 +925,9 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
     cudaError_t e = cudaMemsetAsync(B.counter, 0, 3 * sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     return with_prm(P, [&](auto PT) {
-        if (lane_grid_blocks > 0 && decltype(PT)::kSpecSeeds && PT.mqd <= SPEC_MAX_K) {
+        bool lanes = false;
+        if constexpr (decltype(PT)::kSpecSeeds) lanes = lane_grid_blocks > 0 && PT.mqd <= SPEC_MAX_K;
+        if constexpr (decltype(PT)::kSpecSeeds) if (lanes) {
             // lane per pair; the few pairs that live in the general code are handed to the warp-per-pair walk
             k_walk_lanes<<<lane_grid_blocks, LZ_LANE_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
                                                                      PT, table_pool, B.counter, reinterpret_cast<int3*>(out), B.hard,
@@ -932,7 +937,8 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
             k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
                                                                 PT, bitmap_pool, table_pool, B.counter + 1, reinterpret_cast<int3*>(out),
                                                                 B.hard, B.counter + 2);
-        } else
+        }
+        if (!lanes)
             k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
                                                                 PT, bitmap_pool, table_pool, B.counter, reinterpret_cast<int3*>(out),
                                                                 nullptr, nullptr);

@@ -52,6 +52,14 @@ struct PrmDefault {
     int mrd, mqd, reg;
 };
 LZ_HD bool is_default_kernel_params(const Prm& p) { return p.mal == 11 && p.msl == 7 && p.aw == 15 && p.am == 7 && p.ar == 3; }
+// The long-genome parameters BASELINE configs[4] names for bacterial sets (--mal 15 --msl 9 --aw 20 --am 9 --ar 4),
+// also compile-time for the staged kernels: the run tests of the seed scan (msl) and the extension windows unroll.
+struct PrmLong {
+    static constexpr int mal = 15, msl = 9, aw = 20, am = 9, ar = 4;
+    static constexpr bool kSpecSeeds = false;
+    int mrd, mqd, reg;
+};
+LZ_HD bool is_long_kernel_params(const Prm& p) { return p.mal == 15 && p.msl == 9 && p.aw == 20 && p.am == 9 && p.ar == 4; }
 
 // per-sequence placement in the record pool
 struct SeqMeta {

@@ -147,6 +147,7 @@ extern "C" double lzani_emul_run_rows(const int32_t* p8, uint32_t n_seqs, const 
                 PairResult res;
                 if (staged) {
                     if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = staged_pair(w, pv, D, staged == 2); }
+                    else if (is_long_kernel_params(P)) { const PrmLong D{P.mrd, P.mqd, P.reg}; res = staged_pair(w, pv, D, staged == 2); }
                     else res = staged_pair(w, pv, P, staged == 2);
                 } else if (is_default_kernel_params(P)) { const PrmDefault D{P.mrd, P.mqd, P.reg}; res = parse_pair(w, pv, D, &scratch); }
                 else res = parse_pair(w, pv, P, &scratch);

@@ -95,6 +95,8 @@ def main():
     ap.add_argument("--cpu-pairs", type=int, default=0, help="pairs of the parity / CPU sample per rank (default: 64 / 4)")
     ap.add_argument("--workers", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--pick", choices=["related", "unrelated"], default=None,
+                    help="config 5, diagnostics: only the genomes of one family / one genome per family")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     import torch
@@ -143,6 +145,10 @@ def main():
     else:
         G = a.genomes or 500
         ss, d, fam, new_of_old, order = build_set("bact", G, rank, world, barrier, workers)
+        if a.pick:
+            idx = (np.nonzero(fam == fam[0])[0] if a.pick == "related"
+                   else np.array([np.nonzero(fam == f)[0][0] for f in np.unique(fam)]))
+            ss = PackedSet([ss.names[i] for i in idx], ss.lens[idx], [ss.packed[i] for i in idx])
         n = len(ss)
         params = LONGP
     prep_s = time.perf_counter() - t_prep
