@@ -766,9 +766,8 @@ LZ_HD void lane_slow_step(LaneCtx& L, const PT& P)
                 if (a_pos) {                              // :604
                     if (!best_pos) take_anchor = true;    // :606-610
                     else {
-                        const double pa = ipow_u32(one_minus_4pow(a_len), (uint32_t)(2 * (pv.Dr + 1 - a_len)));
-                        const double pc = ipow_u32(one_minus_4pow(best_len), (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
-                        take_anchor = pa > pc;
+                        take_anchor = anchor_beats_seed(a_len, (uint32_t)(2 * (pv.Dr + 1 - a_len)), best_len,
+                                                        (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
                     }
                 }
                 if (take_anchor) { best_pos = a_pos; best_len = a_len; }

@@ -79,6 +79,18 @@ LZ_HD double ipow_u32(double base, uint32_t e)
     return r;
 }
 
+// The anchor / seed arbitration of parser.cpp:606-610: take the anchor iff pa > pc with
+// pa = (1 - 4^-a_len)^ea, pc = (1 - 4^-best_len)^ec (ea, ec as the reference's uint32).  Two outcomes need no
+// multiplication and are exact: a power of exactly 1.0 (len >= 27, or exponent 0) is exactly 1.0, and a base
+// below 1 raised to an exponent >= 1 stays below 1 (the product of two doubles <= 1 - 2^-53 is at most
+// 1 - 2^-52 + 2^-106, which rounds to 1 - 2^-52, never up to 1.0).  Long anchors in related genomes take them.
+LZ_HD bool anchor_beats_seed(int a_len, uint32_t ea, int best_len, uint32_t ec)
+{
+    if (best_len >= 27 || ec == 0u) return false;        // pc == 1.0 >= pa
+    if (a_len >= 27 || ea == 0u) return true;            // pa == 1.0 > pc
+    return ipow_u32(one_minus_4pow(a_len), ea) > ipow_u32(one_minus_4pow(best_len), ec);
+}
+
 // ---- mismatch streams.  A stream is a virtual bit string (1 = mismatch); stream word `wi`
 // holds stream positions [32*wi, 32*wi+32).
 struct FwdStream {   // position k <-> q[q0+k] vs r[r0+k]
@@ -1933,9 +1945,8 @@ LZ_HD PairResult parse_pair(W& w, const PairView& pv, const PT& P, WarpScratch* 
                 if (a_pos) {                              // :604
                     if (!best_pos) take_anchor = true;    // :606-610
                     else {
-                        const double pa = ipow_u32(one_minus_4pow(a_len), (uint32_t)(2 * (pv.Dr + 1 - a_len)));
-                        const double pc = ipow_u32(one_minus_4pow(best_len), (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
-                        take_anchor = pa > pc;
+                        take_anchor = anchor_beats_seed(a_len, (uint32_t)(2 * (pv.Dr + 1 - a_len)), best_len,
+                                                        (uint32_t)(lit0 + k + P.mrd + 1 - best_len));
                     }
                 }
                 if (take_anchor) { best_pos = a_pos; best_len = a_len; }
