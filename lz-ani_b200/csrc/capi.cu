@@ -81,7 +81,8 @@ struct lzani_ctx {
         uint32_t* h_total = nullptr;      // pinned: records of the chunk
         uint32_t* mc = nullptr;           // all2all scan: bitmap-bit x reference matrix (2^bbits words)
         uint64_t mc_words = 0;
-    } slot[2];
+    } slot[4];
+    int n_slots = 2;                      // chunks in flight (LZANI_SLOTS, 1..4): slot i's walk overlaps the stages and walks of the others
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
     uint64_t staged_words = 0;            // words per chunk (LZANI_STAGED_WORDS; 0: sized from the free HBM at the first run)
@@ -261,6 +262,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
     // fewer resident walk blocks leave registers for the other slot's data-parallel stages to run beside the walk
     if (const char* e = getenv("LZANI_WALK_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->walk_blocks_per_sm) c->walk_blocks_per_sm = v; }
+    if (const char* e = getenv("LZANI_SLOTS")) { const int v = atoi(e); if (v >= 1 && v <= 4) c->n_slots = v; }
     if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) c->staged_words = (uint64_t)v; }
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
@@ -576,12 +578,12 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         }
     }
     if (staged && !c->staged_words) {
-        // chunk size: both slots together may take a fifth of the free HBM (~40 B of scratch per query word),
+        // chunk size: the slots together may take a fifth of the free HBM (~40 B of scratch per query word),
         // between 96 M and 768 M words -- large chunks keep many rows together (the all2all scan handles 32
         // references per gather) and the walk's tails rare; buffers still only grow to what a run needs
         size_t fr = 0, tot = 0;
         LZ_CUDA(c, cudaMemGetInfo(&fr, &tot));
-        uint64_t wds = (uint64_t)((double)fr * 0.2 / 80.0);
+        uint64_t wds = (uint64_t)((double)fr * 0.2 / (40.0 * c->n_slots));
         wds = std::max<uint64_t>(96ull << 20, std::min<uint64_t>(wds, 768ull << 20));
         c->staged_words = wds;
     }
@@ -592,7 +594,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         const uint64_t pcap = std::min<uint64_t>(n_pairs, (uint64_t)1 << 19);
         uint64_t rcap = wcap + wcap / 4 + 1024;
         if (c->staged_recs) rcap = c->staged_recs;       // test knob: forces the chunk-halving / growth paths
-        const int n_slots = words_run > wcap ? 2 : 1;
+        const int n_slots = words_run > wcap ? c->n_slots : 1;
         for (int i = 0; i < n_slots; ++i) {
             lzani_ctx::Slot& sl = c->slot[i];
             if (pcap > sl.pairs_cap || wcap > sl.words_cap || rcap > sl.recs_cap)
@@ -704,7 +706,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                 uint32_t j_cur = b.a;
                 while (k_next < ke || !redo.empty()) {
                     Range ch{0, 0, 0};
-                    lzani_ctx::Slot& sl = c->slot[c->staged_chunks & 1u];
+                    lzani_ctx::Slot& sl = c->slot[c->staged_chunks % (uint32_t)c->n_slots];
                     if (!redo.empty()) { ch = redo.back(); redo.pop_back(); }
                     else {
                         // the next chunk: as many pairs as the word / record / pair capacities allow
@@ -754,11 +756,14 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                             if (mw > sl.mc_words) {
                                 LZ_CUDA(c, cudaStreamSynchronize(sl.st));
                                 cudaFree(sl.mc); sl.mc = nullptr; sl.mc_words = 0;
-                                LZ_CUDA(c, cudaMalloc((void**)&sl.mc, sizeof(uint32_t) * mw));
-                                sl.mc_words = mw;
+                                // no room for the matrix (up to 4 GB): not an error, the probe scan does the chunk
+                                if (cudaMalloc((void**)&sl.mc, sizeof(uint32_t) * mw) == cudaSuccess) sl.mc_words = mw;
+                                else { sl.mc = nullptr; (void)cudaGetLastError(); }
                             }
-                            mx.mc = sl.mc; mx.bbits = bb; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
-                            use_mx = true;
+                            if (sl.mc) {
+                                mx.mc = sl.mc; mx.bbits = bb; mx.row_first = ja - b.a; mx.n_rows_chunk = jb - ja; mx.n_seqs = n; mx.max_words = words_max;
+                                use_mx = true;
+                            }
                         }
                     }
                     LZ_CUDA(c, launch_staged_scan(sl.st, sl.B, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,

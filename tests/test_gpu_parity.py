@@ -174,6 +174,21 @@ def test_megabase_genomes_config5(params):
     assert np.array_equal(got, want), f"{got.tolist()} vs {want.tolist()}"
 
 
+def test_five_megabase_genomes_full_config5_length():
+    """BASELINE configs[4] at its real genome length: 5 Mb genomes, long-genome parameters -- a related pair (4 %
+    divergence, block events), and an unrelated genome of the same size (so all bitmaps have one size and the hashed
+    form of the all2all scan runs; 2^29-bit bitmaps, 2^25-slot tables) -- all six ordered pairs against the oracle."""
+    rng = np.random.default_rng(56)
+    root = rng.integers(0, 4, size=5_000_000, dtype=np.uint8)
+    other = rng.integers(0, 4, size=4_900_000, dtype=np.uint8)
+    seqs = [root, synth._mutate(rng, root, 0.04, block=(5000, 50000), p_block=1.0), other]
+    ss = hostio.SeqSet(["root", "m4", "other"], seqs)
+    got, t = run_gpu(ss, mg.LONGP)
+    want = Oracle().run_rows(ss, mg.LONGP, threads=6)
+    assert np.array_equal(got, want), f"{got.tolist()} vs {want.tolist()}"
+    assert got[0, 0] > 4_000_000 and got[1, 0] < 100_000       # root-m4 aligns almost everywhere, root-other nowhere
+
+
 @pytest.mark.parametrize("sname,params", [("example", None), ("example", mg.ODD), ("synth_small", mg.LONGP)])
 def test_region_records_match_oracle(sname, params):
     """--out-alignment path (lzani_run_rows_regions, replaces CParser::get_parsing): counts and region
