@@ -86,6 +86,7 @@ struct lzani_ctx {
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
     uint64_t staged_words = 0;            // words per chunk (LZANI_STAGED_WORDS; 0: sized from the free HBM at the first run)
+    bool staged_words_fixed = false;      // set by LZANI_STAGED_WORDS: chunks never grow beyond it
     uint64_t staged_recs = 0;             // record capacity per chunk (LZANI_STAGED_RECS; 0: 1.25 per word)
     int walk_blocks_per_sm = 1;
     int lane_walk = 1;                    // 0: warp-per-pair walk k_walk_pairs (LZANI_LANE_WALK=0)
@@ -263,7 +264,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     // fewer resident walk blocks leave registers for the other slot's data-parallel stages to run beside the walk
     if (const char* e = getenv("LZANI_WALK_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->walk_blocks_per_sm) c->walk_blocks_per_sm = v; }
     if (const char* e = getenv("LZANI_SLOTS")) { const int v = atoi(e); if (v >= 1 && v <= 4) c->n_slots = v; }
-    if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) c->staged_words = (uint64_t)v; }
+    if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) { c->staged_words = (uint64_t)v; c->staged_words_fixed = true; } }
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
         LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
@@ -713,6 +714,12 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         uint64_t w_target = c->staged_words;
                         const uint64_t have_r = sl.recs_cap ? sl.recs_cap : c->slot[0].recs_cap;
                         const uint64_t by_recs = (uint64_t)((double)have_r / (1.15 * c->rec_per_word));
+                        // long genomes: a chunk of the configured size holds few pairs (about one wave of the walk) and few
+                        // rows (the all2all scan costs the same for 3 rows as for 32).  Once the hit density has been
+                        // observed, such chunks grow to what the record buffers hold at that density -- only the 12 B
+                        // per word of hit masks / offsets grow with them -- up to twice the configured words.
+                        if (c->staged_chunks > 0 && !c->staged_words_fixed && words_run / std::max<uint64_t>(n_pairs, 1) * 32768ull > c->staged_words)
+                            w_target = std::min<uint64_t>(2 * c->staged_words, 0xE0000000ull);
                         if (by_recs < w_target) w_target = by_recs;
                         const uint64_t p_max = (uint64_t)1 << 19;
                         uint64_t k = k_next, wsum = 0;
