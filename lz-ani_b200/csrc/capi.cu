@@ -78,6 +78,8 @@ struct lzani_ctx {
         uint64_t pairs_cap = 0, words_cap = 0, recs_cap = 0;
         cudaStream_t st = nullptr;
         cudaEvent_t done = nullptr;
+        cudaEvent_t dbg[4] = {nullptr, nullptr, nullptr, nullptr};   // LZANI_DEBUG_CHUNKS: scan start / scan end / walk start / walk end
+        uint32_t dbg_chunk = 0; bool dbg_set = false;
         uint32_t* h_total = nullptr;      // pinned: records of the chunk
         uint32_t* mc = nullptr;           // all2all scan: bitmap-bit x reference matrix (2^bbits words)
         uint64_t mc_words = 0;
@@ -86,6 +88,9 @@ struct lzani_ctx {
     int matrix_scan = 1;                  // 0: always the probe scan (LZANI_MATRIX_SCAN=0)
     int staged = 1;                       // 0: one-kernel parse (LZANI_STAGED=0)
     uint64_t staged_words = 0;            // words per chunk (LZANI_STAGED_WORDS; 0: sized from the free HBM at the first run)
+    bool debug_chunks = false;            // LZANI_DEBUG_CHUNKS=1: one line per chunk on stderr
+    bool density_seen = false;            // rec_per_word is an observation, not the initial guess
+    uint64_t staged_grow = 0;             // words per chunk after the one-time growth for long genomes (0: not grown)
     bool staged_words_fixed = false;      // set by LZANI_STAGED_WORDS: chunks never grow beyond it
     uint64_t staged_recs = 0;             // record capacity per chunk (LZANI_STAGED_RECS; 0: 1.25 per word)
     int walk_blocks_per_sm = 1;
@@ -134,6 +139,7 @@ void free_sequences(lzani_ctx* c)
     c->src_cap = c->meta_cap = c->recs_cap = c->h_src_cap = 0;
     c->n_seqs = 0; c->n_recs = 0; c->meta.clear();
     c->last_valid = false;
+    c->staged_grow = 0; c->density_seen = false; c->rec_per_word = 1.0;      // chunk sizing observations belong to a set
 }
 
 void free_slot(lzani_ctx::Slot& s)
@@ -263,11 +269,13 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
     if (const char* e = getenv("LZANI_MATRIX_SCAN")) c->matrix_scan = atoi(e);
     // fewer resident walk blocks leave registers for the other slot's data-parallel stages to run beside the walk
     if (const char* e = getenv("LZANI_WALK_BLOCKS")) { const int v = atoi(e); if (v > 0 && v < c->walk_blocks_per_sm) c->walk_blocks_per_sm = v; }
+    if (const char* e = getenv("LZANI_DEBUG_CHUNKS")) c->debug_chunks = atoi(e) != 0;
     if (const char* e = getenv("LZANI_SLOTS")) { const int v = atoi(e); if (v >= 1 && v <= 4) c->n_slots = v; }
     if (const char* e = getenv("LZANI_STAGED_WORDS")) { const long long v = atoll(e); if (v > 0) { c->staged_words = (uint64_t)v; c->staged_words_fixed = true; } }
     for (auto& sl : c->slot) {
         LZ_CUDA(c, cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
         LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+        for (auto& e : sl.dbg) LZ_CUDA(c, cudaEventCreate(&e));
         LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, 4 * sizeof(uint32_t)));
         LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, 4 * sizeof(unsigned long long)));
     }
@@ -294,6 +302,7 @@ extern "C" void lzani_destroy(lzani_ctx* c)
             cudaFree(sl.B.counter);
             if (sl.h_total) cudaFreeHost(sl.h_total);
             if (sl.done) cudaEventDestroy(sl.done);
+            for (auto& e : sl.dbg) if (e) cudaEventDestroy(e);
             if (sl.st) cudaStreamDestroy(sl.st);
         }
         for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -718,8 +727,13 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         // rows (the all2all scan costs the same for 3 rows as for 32).  Once the hit density has been
                         // observed, such chunks grow to what the record buffers hold at that density -- only the 12 B
                         // per word of hit masks / offsets grow with them -- up to twice the configured words.
-                        if (c->staged_chunks > 0 && !c->staged_words_fixed && words_run / std::max<uint64_t>(n_pairs, 1) * 32768ull > c->staged_words)
-                            w_target = std::min<uint64_t>(2 * c->staged_words, 0xE0000000ull);
+                        // Decided ONCE (growing a buffer means cudaFree, which waits for the other slot's walk).
+                        if (!c->staged_grow && c->density_seen && !c->staged_words_fixed &&
+                            words_run / std::max<uint64_t>(n_pairs, 1) * 32768ull > c->staged_words) {
+                            c->staged_grow = std::min<uint64_t>(std::min<uint64_t>(2 * c->staged_words, 0xE0000000ull), by_recs);
+                            if (c->staged_grow < c->staged_words) c->staged_grow = c->staged_words;
+                        }
+                        if (c->staged_grow) w_target = c->staged_grow;
                         if (by_recs < w_target) w_target = by_recs;
                         const uint64_t p_max = (uint64_t)1 << 19;
                         uint64_t k = k_next, wsum = 0;
@@ -744,9 +758,21 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     if (np > sl.pairs_cap || ch.words > sl.words_cap || !sl.recs_cap) {
                         LZ_CUDA(c, cudaStreamSynchronize(sl.st));
                         if (int rc = ensure_slot(c, sl, std::max(np, std::max(sl.pairs_cap, c->slot[0].pairs_cap)),
-                                                 std::max(ch.words, std::max(sl.words_cap, c->slot[0].words_cap)),
+                                                 std::max(std::max(ch.words, c->staged_grow), std::max(sl.words_cap, c->slot[0].words_cap)),
                                                  std::max(sl.recs_cap, c->slot[0].recs_cap))) return rc;
                     }
+                    auto dbg_report = [&](lzani_ctx::Slot& s_) {
+                        if (!c->debug_chunks || !s_.dbg_set) return;
+                        cudaEventSynchronize(s_.dbg[3]);
+                        float t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+                        cudaEventElapsedTime(&t0, c->ev[4], s_.dbg[0]); cudaEventElapsedTime(&t1, c->ev[4], s_.dbg[1]);
+                        cudaEventElapsedTime(&t2, c->ev[4], s_.dbg[2]); cudaEventElapsedTime(&t3, c->ev[4], s_.dbg[3]);
+                        fprintf(stderr, "[lzani] chunk %u timeline (ms since the batch's index): scan %.1f-%.1f  records+walk %.1f-%.1f\n",
+                                s_.dbg_chunk, t0, t1, t2, t3);
+                        s_.dbg_set = false;
+                    };
+                    dbg_report(sl);
+                    if (c->debug_chunks) LZ_CUDA(c, cudaEventRecord(sl.dbg[0], sl.st));
                     // all2all form of the scan when the chunk is made of whole dense rows and the bitmaps are direct
                     MatrixScan mx{};
                     bool use_mx = false;
@@ -776,6 +802,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     LZ_CUDA(c, launch_staged_scan(sl.st, sl.B, c->d_recs, c->d_meta, c->d_row_ref + b.a, c->d_row_idx + b.a,
                                                   c->d_row_off + b.a, nb, q_ids ? c->d_q_ids : nullptr, ch.k0, (uint32_t)np,
                                                   ch.words, P, c->d_bitmap, c->n_sm, use_mx ? &mx : nullptr));
+                    if (c->debug_chunks) LZ_CUDA(c, cudaEventRecord(sl.dbg[1], sl.st));
                     LZ_CUDA(c, cudaMemcpyAsync(sl.h_total, sl.B.rec_off + ch.words, sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.st));
                     // rec_off is a 32-bit scan: a word holds up to 16 hit runs, so beyond 2^28 words the total could wrap --
                     // such chunks also get the exact 64-bit count (one more pass over the hit masks, ~0.5 ms)
@@ -794,9 +821,14 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                     T.launches += 1 + (ch.words ? (use_mx ? 2 * ((mx.n_rows_chunk + 31) / 32) : 1) : 0);     // our kernels (CUB's scans not counted)
                     if (ch.words) {
                         const double ratio = (double)n_hit / (double)ch.words;
-                        c->rec_per_word = ratio > c->rec_per_word ? ratio : 0.5 * (c->rec_per_word + ratio);
+                        c->rec_per_word = ratio > c->rec_per_word || !c->density_seen ? ratio : 0.5 * (c->rec_per_word + ratio);
+                        c->density_seen = true;
                         if (c->rec_per_word < 0.25) c->rec_per_word = 0.25;
                     }
+                    if (c->debug_chunks)
+                        fprintf(stderr, "[lzani] chunk %u slot %u: pairs %llu words %llu hit runs %llu (capacity %llu)%s\n", c->staged_chunks,
+                                c->staged_chunks % (uint32_t)c->n_slots, (unsigned long long)np, (unsigned long long)ch.words,
+                                (unsigned long long)n_hit, (unsigned long long)sl.recs_cap, n_hit > sl.recs_cap ? "  -> halved" : "");
                     if (n_hit > sl.recs_cap || n_hit > 0xFFFFFFFFull) {
                         if (np > 1) {                      // too many hit runs for the record buffers: halve the chunk
                             const uint64_t mid = ch.k0 + np / 2;
@@ -808,9 +840,11 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                         if (n_hit > 0xFFFFFFFFull) return fail(c, LZANI_ERR_NOMEM, "one pair has more than 2^32 hit runs");
                         if (int rc = ensure_slot(c, sl, sl.pairs_cap, sl.words_cap, n_hit)) return rc;
                     }
+                    if (c->debug_chunks) LZ_CUDA(c, cudaEventRecord(sl.dbg[2], sl.st));
                     LZ_CUDA(c, launch_staged_walk(sl.st, wgrid, sl.B, c->d_recs, ch.k0, (uint32_t)np, ch.words, n_hit, P,
                                                   c->d_bitmap, c->d_table, c->d_out,
                                                   c->lane_walk ? c->n_sm * c->lane_blocks_per_sm : 0));
+                    if (c->debug_chunks) { LZ_CUDA(c, cudaEventRecord(sl.dbg[3], sl.st)); sl.dbg_chunk = c->staged_chunks; sl.dbg_set = true; }
                     T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 1) : 0) +
                                   (c->lane_walk && is_default_kernel_params(P) && P.mqd <= 57 ? 1 : 0);
                     ++c->staged_chunks;
