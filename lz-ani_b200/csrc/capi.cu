@@ -277,7 +277,7 @@ extern "C" int lzani_create(lzani_ctx** out, const lzani_params_t* p, const int*
         LZ_CUDA(c, cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
         for (auto& e : sl.dbg) LZ_CUDA(c, cudaEventCreate(&e));
         LZ_CUDA(c, cudaMallocHost((void**)&sl.h_total, 4 * sizeof(uint32_t)));
-        LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, 4 * sizeof(unsigned long long)));
+        LZ_CUDA(c, cudaMalloc((void**)&sl.B.counter, 6 * sizeof(unsigned long long)));
     }
     return LZANI_OK;
 }
@@ -846,7 +846,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
                                                   c->lane_walk ? c->n_sm * c->lane_blocks_per_sm : 0));
                     if (c->debug_chunks) { LZ_CUDA(c, cudaEventRecord(sl.dbg[3], sl.st)); sl.dbg_chunk = c->staged_chunks; sl.dbg_set = true; }
                     T.launches += 1 + (ch.words ? 1 : 0) + (n_hit ? (is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 1) : 0) +
-                                  (c->lane_walk && is_default_kernel_params(P) && P.mqd <= 57 ? 1 : 0);
+                                  (c->lane_walk && is_default_kernel_params(P) && P.mqd <= 57 ? 2 : 0);
                     ++c->staged_chunks;
                 }
                 for (auto& sl : c->slot) {

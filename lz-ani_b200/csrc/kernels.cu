@@ -530,14 +530,46 @@ __device__ __forceinline__ void lane_ctx_load(const LaneSlots& m, int j, LaneCtx
     L.mode = mode;
 }
 
+// Related genomes show in the hit records before any walking: an unrelated pair has about 32 * rho * (1 - rho) hit
+// runs per 32 query positions, rho = the share of all mal-mers the reference holds.  A pair with LZ_LANE_DENSE_PCT %
+// of that or more is a related one.
+template <class PT>
+__device__ __forceinline__ bool pair_is_dense(const PT& P, const PairDesc& pd, uint32_t nw, uint32_t n_rec)
+{
+    const float rho = fminf(1.0f, (float)pd.Dr * exp2f(-2.0f * (float)P.mal));
+    return (float)n_rec * 100.0f > (float)LZ_LANE_DENSE_PCT * 32.0f * rho * (1.0f - rho) * (float)nw + 6400.0f;
+}
+
+// how many pairs of the chunk are related ones (decides whether k_walk_lanes hands them over, see LZ_LANE_KEEP_DEN)
+template <class PT>
+__global__ void __launch_bounds__(256)
+k_count_dense(const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off, const uint32_t* __restrict__ rec_off,
+              uint32_t n_pairs, PT P, unsigned long long* __restrict__ n_dense)
+{
+    const uint32_t pl = blockIdx.x * 256u + threadIdx.x;
+    bool dense = false;
+    if (pl < n_pairs) {
+        const uint32_t w0 = word_off[pl], w1 = word_off[pl + 1];
+        dense = pair_is_dense(P, desc[pl], w1 - w0, rec_off[w1] - rec_off[w0]);
+    }
+    const int c = __syncthreads_count(dense);
+    if (threadIdx.x == 0 && c) atomicAdd(n_dense, (unsigned long long)c);
+}
+
 template <class PT>
 __global__ void __launch_bounds__(LZ_LANE_THREADS, LZ_LANE_MIN_BLOCKS)
 k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, const uint32_t* __restrict__ word_off,
              const uint32_t* __restrict__ rec_off, const Rec* __restrict__ hit_recs, uint32_t n_pairs,
              uint64_t pair_begin, PT P, const uint64_t* __restrict__ table_pool, unsigned long long* __restrict__ counter,
-             int3* __restrict__ out, uint32_t* __restrict__ hard_list, unsigned long long* __restrict__ hard_count)
+             int3* __restrict__ out, uint32_t* __restrict__ hard_list, unsigned long long* __restrict__ hard_count,
+             const unsigned long long* __restrict__ n_dense)
 {
     __shared__ LaneSlots slots;
+    // related pairs go to the warp-per-pair walk only while they are the exception in this chunk (the flag is read in
+    // two rare places: shared memory, not a register of the hot loop)
+    __shared__ int s_hand_over;
+    if (threadIdx.x == 0) s_hand_over = *n_dense * (unsigned long long)LZ_LANE_KEEP_DEN <= (unsigned long long)n_pairs;
+    __syncthreads();
     int mode[LZ_LANE_SLOTS];
 #pragma unroll
     for (int j = 0; j < LZ_LANE_SLOTS; ++j) mode[j] = LANE_DONE;
@@ -556,13 +588,8 @@ k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
                         const uint32_t pl = (uint32_t)k;
                         const uint32_t r0 = rec_off[word_off[pl]], r1 = rec_off[word_off[pl + 1]];
                         const PairDesc pd = desc[pl];
-                        // Related genomes show in the hit records before any walking: an unrelated pair has about
-                        // 32 * rho * (1 - rho) hit runs per 32 query positions, rho = the share of all mal-mers the reference
-                        // holds.  A pair with LZ_LANE_DENSE_PCT % of that or more would only park its way to the hand-over:
-                        // it goes to the warp-per-pair walk at once.
-                        const uint32_t nw = word_off[pl + 1] - word_off[pl];
-                        const float rho = fminf(1.0f, (float)pd.Dr * exp2f(-2.0f * (float)P.mal));
-                        if ((float)(r1 - r0) * 100.0f > (float)LZ_LANE_DENSE_PCT * 32.0f * rho * (1.0f - rho) * (float)nw + 6400.0f) {
+                        // a related pair would only park its way to the hand-over: it goes to the warp-per-pair walk at once
+                        if (s_hand_over && pair_is_dense(P, pd, word_off[pl + 1] - word_off[pl], r1 - r0)) {
                             hard_list[atomicAdd(hard_count, 1ull)] = pl;
                             mode[j] = LANE_DONE;        // the slot takes another pair next round
                             live = true;
@@ -620,7 +647,8 @@ k_walk_lanes(const Rec* __restrict__ recs, const PairDesc* __restrict__ desc, co
                 uint32_t r0, pl;
                 int parks;
                 lane_ctx_load(slots, js, L, hit_recs, r0, pl, parks, LANE_SLOW);
-                if (++parks > LZ_LANE_HARD_BASE + (L.n_loop >> LZ_LANE_HARD_SHIFT) && L.s.i < L.n_loop) {
+                ++parks;
+                if (parks > LZ_LANE_HARD_BASE + (L.n_loop >> LZ_LANE_HARD_SHIFT) && L.s.i < L.n_loop && s_hand_over) {
                     hard_list[atomicAdd(hard_count, 1ull)] = pl;       // k_walk_pairs restarts it
                     L.mode = LANE_DONE;
                 } else {
@@ -921,17 +949,23 @@ cudaError_t launch_staged_walk(cudaStream_t st, int grid_blocks, const StagedBuf
         });
         if (e != cudaSuccess) return e;
     }
-    // counter[0]: pairs pulled by the first walk kernel, [1]: by the second, [2]: pairs handed over
+    // counter[0]: pairs pulled by the first walk kernel, [1]: by the second, [2]: pairs handed over, [4]: related pairs
+    // of the chunk ([3] is launch_run_total's)
     cudaError_t e = cudaMemsetAsync(B.counter, 0, 3 * sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(B.counter + 4, 0, sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     return with_prm(P, [&](auto PT) {
         bool lanes = false;
         if constexpr (decltype(PT)::kSpecSeeds) lanes = lane_grid_blocks > 0 && PT.mqd <= SPEC_MAX_K;
         if constexpr (decltype(PT)::kSpecSeeds) if (lanes) {
             // lane per pair; the few pairs that live in the general code are handed to the warp-per-pair walk
+            k_count_dense<<<n_pairs / 256 + 1, 256, 0, st>>>(B.desc, B.word_off, B.rec_off, n_pairs, PT, B.counter + 4);
+            const cudaError_t e0 = cudaGetLastError();
+            if (e0 != cudaSuccess) return e0;
             k_walk_lanes<<<lane_grid_blocks, LZ_LANE_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
                                                                      PT, table_pool, B.counter, reinterpret_cast<int3*>(out), B.hard,
-                                                                     B.counter + 2);
+                                                                     B.counter + 2, B.counter + 4);
             const cudaError_t e1 = cudaGetLastError();
             if (e1 != cudaSuccess) return e1;
             k_walk_pairs<<<grid_blocks, LZ_WALK_THREADS, 0, st>>>(recs, B.desc, B.word_off, B.rec_off, B.recs, n_pairs, pair_begin,
