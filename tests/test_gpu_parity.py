@@ -132,6 +132,26 @@ def test_properties_at_bench_scale():
         m.close()
 
 
+def test_related_pairs_as_the_exception_and_as_the_rule(monkeypatch):
+    """The lane walk hands related pairs to the warp-per-pair walk while they are at most a quarter of a chunk and keeps
+    them otherwise (k_count_dense).  Both regimes, against the oracle on sampled rows and against the warp-per-pair
+    walk (LZANI_LANE_WALK=0) on every pair: 160 genomes in families of 20 (12 % related pairs: handed over) and the
+    first 40 of them in one chunk (49 % related: kept)."""
+    names, seqs = synth.viral(160, seed=synth.SEED + 9)
+    for count in (160, 40):
+        ss = hostio.SeqSet(list(names[:count]), list(seqs[:count]))
+        n = len(ss)
+        monkeypatch.setenv("LZANI_LANE_WALK", "1")
+        got, _ = run_gpu(ss, None)
+        monkeypatch.setenv("LZANI_LANE_WALK", "0")
+        warp, _ = run_gpu(ss, None)
+        bad = np.nonzero((got != warp).any(axis=1))[0]
+        assert bad.size == 0, f"{count} genomes: {bad.size} pairs differ between the two walks, first {bad[:5]}"
+        rows = np.array([0, n // 3, n - 1], dtype=np.uint32)
+        want = Oracle().run_rows(ss, None, rows=rows)
+        assert np.array_equal(np.concatenate([got[r * (n - 1):(r + 1) * (n - 1)] for r in rows]), want), count
+
+
 def test_sparse_filter_style_pair_list_config4():
     """BASELINE configs[3] shape at test size: a --flt-kmerdb-style sparse pair list (within-family
     pairs plus a few cross-family decoys, unsorted inside a row as filter rows are) through the CSR
