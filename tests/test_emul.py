@@ -49,10 +49,20 @@ def test_kernel_source_matches_reference_golden(emul, case):
     (28, dict(mal=11, msl=7, mrd=60, mqd=90, reg=35, aw=15, am=7, ar=3)),     # default k-mers, window too long for seed records
     (29, dict(mal=11, msl=7, mrd=10, mqd=57, reg=20, aw=15, am=7, ar=3)),     # seed records at their longest scan, two-word rows
     (30, dict(mal=11, msl=7, mrd=70, mqd=20, reg=35, aw=15, am=7, ar=3)),     # three-word rows from the start
+    (31, mg.LONGP),                                                           # the compile-time long-genome set (PrmLong)
+    (32, dict(mal=15, msl=9, mrd=40, mqd=120, reg=60, aw=20, am=9, ar=4)),    # PrmLong with other run-time mrd / mqd / reg
 ])
 def test_kernel_source_vs_oracle_on_fresh_inputs(emul, seed, params):
     names, seqs = synth.families(2, 4, 1500, 4000, seed=seed, block=(100, 400))
     ss = hostio.SeqSet(names, seqs)
+    assert np.array_equal(emul.run_rows(ss, params), Oracle().run_rows(ss, params))
+
+
+@pytest.mark.parametrize("params", [mg.LONGP, dict(mal=15, msl=9, mrd=40, mqd=120, reg=60, aw=20, am=9, ar=4)])
+def test_long_genome_parameter_set_on_edge_cases(emul, params):
+    """PrmLong (compile-time mal 15 / msl 9 / aw 20 / am 9 / ar 4) on the edge set: N runs, sequences shorter than an
+    anchor, identical and reverse-complement pairs."""
+    ss = mg.get_set("edge")
     assert np.array_equal(emul.run_rows(ss, params), Oracle().run_rows(ss, params))
 
 

@@ -46,6 +46,7 @@ def test_cuda_matches_reference_golden(case):
     (40, dict(mal=11, msl=7, mrd=70, mqd=20, reg=35, aw=15, am=7, ar=3)),     # three-word rows from the start
     (34, dict(mal=11, msl=11, mrd=100, mqd=200, reg=35, aw=15, am=15, ar=3)),
     (35, dict(mal=15, msl=9, mrd=80, mqd=80, reg=100, aw=20, am=9, ar=4)),
+    (41, dict(mal=15, msl=9, mrd=40, mqd=120, reg=60, aw=20, am=9, ar=4)),    # PrmLong with other run-time mrd / mqd / reg
 ])
 def test_cuda_vs_oracle_on_fresh_families(seed, params):
     names, seqs = synth.families(3, 5, 4000, 9000, seed=seed, block=(200, 900))
