@@ -107,10 +107,16 @@ enum {
 
 typedef struct lzani_ctx lzani_ctx;
 
-/* Replaces `CParser parser(params)` (parser.h:237-241).  device_ids/n_devices: the CUDA
- * device this context drives (n_devices must be 1: one context -- and one process -- per
- * GPU; device_ids==NULL means the current device).  Returns LZANI_OK or an error code; on
- * error *ctx is still a valid object holding the message when allocation was possible. */
+/* Replaces `CParser parser(params)` and the worker pool around it (parser.h:237-241,
+ * lz_matcher.cpp:184-200).  device_ids/n_devices: the CUDA devices this context drives.
+ * n_devices == 1 (device_ids==NULL: the current device): one context per GPU, e.g. one per
+ * process under torchrun.  n_devices > 1: ONE context that owns all the listed GPUs of the
+ * box -- the library runs one worker thread per device, replicates the sequences, deals
+ * the reference rows of every lzani_run* call over the devices (dense lists: row r to
+ * device r mod n; sparse lists: heaviest rows first) and writes the results back in the
+ * caller's CSR order; lzani_filter_pairs() on such a context reads the other devices' rows
+ * over NVLink peer access.  Returns LZANI_OK or an error code; on error *ctx is still a
+ * valid object holding the message when allocation was possible. */
 int lzani_create(lzani_ctx** ctx, const lzani_params_t* params, const int* device_ids, int n_devices);
 
 /* Replaces the seq_view hand-off of prepare_reference/prepare_data (parser.cpp:16-50).
