@@ -433,7 +433,10 @@ def main():
                 "frac": achieved / peak, "traffic": measured_traffic(n, world) if staged else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": parse_ms / args.steps,
                 "index_kernel_ms": index_ms / args.steps,
-                "index_algorithmic_bytes": BYTES_PER_REF_POS * r_bases}
+                "index_algorithmic_bytes": BYTES_PER_REF_POS * r_bases,
+                "note": "HBM is the contract's denominator; the largest kernel (k_hit_spec, 36 % of the step) is bound by the "
+                        "integer pipe (LOP3/SHF at half rate: ALU pipe 90 % busy), the step issues 403 G warp-instructions "
+                        "= 51 % of the chip's issue rate (DESIGN.md section 8, profiles/r02u_spec_probe_by_function.txt)"}
 
     # ---- parity, on EVERY rank: (1) a bounded sample of this rank's own rows against the reference CParser on the host
     # cores; (2) at 2 000 genomes every result of this rank against the reference's committed per-row digests
