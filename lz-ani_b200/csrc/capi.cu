@@ -593,7 +593,7 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         // references per gather) and the walk's tails rare; buffers still only grow to what a run needs
         size_t fr = 0, tot = 0;
         LZ_CUDA(c, cudaMemGetInfo(&fr, &tot));
-        uint64_t wds = (uint64_t)((double)fr * 0.2 / (40.0 * c->n_slots));
+        uint64_t wds = (uint64_t)((double)fr * 0.2 / ((q_ids ? 60.0 : 40.0) * c->n_slots));     // sparse lists: twice the records (below)
         wds = std::max<uint64_t>(96ull << 20, std::min<uint64_t>(wds, 768ull << 20));
         c->staged_words = wds;
     }
@@ -602,7 +602,10 @@ int run_rows_impl(lzani_ctx* c, uint32_t n_rows, const uint32_t* ref_ids, const 
         else for (uint32_t j = 0; j < n_rows; ++j) words_run += words_all - wq[row_ref[j]];
         const uint64_t wcap = std::max<uint64_t>(std::min<uint64_t>(c->staged_words, words_run), std::max<uint32_t>(words_max, 1u));
         const uint64_t pcap = std::min<uint64_t>(n_pairs, (uint64_t)1 << 19);
-        uint64_t rcap = wcap + wcap / 4 + 1024;
+        // 1.25 hit runs per query word hold any mix of mostly unrelated pairs (0.5 at the bench config).  A sparse pair list
+        // comes from a similarity filter: its pairs are related ones (1.2-1.3 runs per word for phages at >= 70 % identity,
+        // up to 4 for near-identical genomes) -- twice the room, so that the first chunk does not overflow and get re-scanned
+        uint64_t rcap = (q_ids ? 2 * wcap : wcap + wcap / 4) + 1024;
         if (c->staged_recs) rcap = c->staged_recs;       // test knob: forces the chunk-halving / growth paths
         const int n_slots = words_run > wcap ? c->n_slots : 1;
         for (int i = 0; i < n_slots; ++i) {
