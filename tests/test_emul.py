@@ -101,6 +101,43 @@ def test_kernel_source_randomized_differential(emul, seed):
     assert np.array_equal(emul.run_rows(ss, None, threads=4), Oracle().run_rows(ss, None, threads=4))
 
 
+@pytest.mark.parametrize("seed", list(range(200, 216)))
+def test_kernel_source_random_parameters_differential(emul, seed):
+    """Random parameter sets inside the library's limits (mal, msl <= 32; aw, ar <= 32; am >= 0) on small related
+    families with indels, block events and an N run: the kernel source against the oracle, every form of the parse.
+    Draws include msl > mal, am >= aw (the window never breaks), mqd 0, reg 1 and windows far longer than a record."""
+    rng = np.random.default_rng(seed)
+    mal = int(rng.integers(3, 19))
+    # msl <= 12: the reference (and the oracle after it) allocates a direct table of 4^msl entries for the seeds
+    params = dict(mal=mal, msl=int(rng.integers(2, min(mal + 3, 13))), mrd=int(rng.integers(1, 120)), mqd=int(rng.integers(0, 130)),
+                  reg=int(rng.integers(1, 90)), aw=int(rng.integers(1, 33)), am=int(rng.integers(0, 14)), ar=int(rng.integers(1, 7)))
+    names, seqs = synth.families(2, 3, 900, 2600, seed=seed, d_lo=0.0 if seed % 4 == 0 else 0.02,
+                                 d_hi=[0.06, 0.2, 0.4][seed % 3], block=(60, 300))
+    seqs = [s.copy() for s in seqs]
+    a = int(rng.integers(0, 400))
+    seqs[1][a:a + int(rng.integers(1, 40))] = 4          # an N run inside one member
+    ss = hostio.SeqSet(names, seqs)
+    got, want = emul.run_rows(ss, params, threads=4), Oracle().run_rows(ss, params, threads=4)
+    assert np.array_equal(got, want), params
+
+
+@pytest.mark.parametrize("seed", list(range(230, 246)))
+def test_lane_walk_random_window_parameters_differential(emul, seed):
+    """The default k-mer / extension constants (the parameter sets the lane walk and the seed records exist for) with
+    random run-time mrd / mqd / reg: windows of two and three words, windows too wide for a seed record (mrd + mqd + 6 >
+    96: the lane scans diagonals), mqd beyond SPEC_MAX_K (no lane walk), reg 1."""
+    rng = np.random.default_rng(seed)
+    params = dict(mal=11, msl=7, mrd=int(rng.integers(1, 110)), mqd=int(rng.integers(0, 70)), reg=int(rng.integers(1, 80)),
+                  aw=15, am=7, ar=3)
+    names, seqs = synth.families(2, 4, 1500, 5000, seed=seed, d_lo=0.0 if seed % 4 == 0 else 0.02,
+                                 d_hi=[0.06, 0.2, 0.4][seed % 3], block=(60, 300))
+    seqs = [s.copy() for s in seqs]
+    a = int(rng.integers(0, 900))
+    seqs[2][a:a + int(rng.integers(1, 60))] = 4
+    ss = hostio.SeqSet(names, seqs)
+    assert np.array_equal(emul.run_rows(ss, params, threads=4), Oracle().run_rows(ss, params, threads=4)), params
+
+
 @pytest.mark.parametrize("sname,params", [("example", None), ("example", mg.ODD), ("edge", None), ("synth_small", mg.LONGP)])
 def test_region_fold_matches_oracle_regions(emul, sname, params):
     """--out-alignment path: the streaming region fold of the kernel source (regions.h) against the
