@@ -1,11 +1,5 @@
 // lane_walk.h -- the sequential walk of the staged parse, ONE LANE PER PAIR.
 //
-// Launched (and emulated in tests/emul) only for the parameter sets that have seed records: PrmDefault's k-mer /
-// extension constants (mal 11, msl 7, aw 15, am 7, ar 3) with any mrd / reg and mqd <= SPEC_MAX_K; every other set
-// is walked one warp per pair (parse_core.h).  The code is written against P.mal, P.msl, ... but only that
-// instantiation is validated: a differential run with mal = 5 (anchors shorter than seeds, a hit at every position)
-// disagrees with the oracle in ~2 % of the pairs, while mal = 6..12 agree.
-//
 // parse_core.h's parse_pair() gives a whole warp to one pair: its lanes cooperate on the rare wide
 // operations (long matches, diagonal scans) but execute the state machine of parser.cpp:501-708 itself --
 // which record comes next, is it plain, region bookkeeping -- 32 times over (ncu r01zg: ~60 % of the walk's
