@@ -614,7 +614,9 @@ LZ_HD void lane_run_step(LaneCtx& L, const PT& P, const RecAhead& ahead)
             s.lit = 0;
             s.re = s.i;
             lane_set_spec(L, w2, w3);
-            L.c = ev.idx + 1u;
+            // the record is behind the walk now -- unless the match is shorter than the record's run of hits, which takes
+            // mal <= 7 (a match is at least mal long, a run at most 8): then the walk stands inside that run
+            L.c = (P.mal <= 7 && qi + (int)((w2 >> HIT_RUN_SHIFT) & 7u) >= s.i) ? ev.idx : ev.idx + 1u;
             // (run > 0: the region just opened is the one the record's fields describe -- what verified_link assumed)
             if (run > 0 && L.spec_K1 > 0) L.chain = (int)ev.link;
             return;

@@ -100,10 +100,10 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P, bool lane_w
     }
     for (size_t t = 0; t < list.size(); ++t)
         recs[t].x = (recs[t].x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) | (link[t] << HIT_ENTRY_RUN_SHIFT);
-    // k_walk_lanes (one lane per pair, lane_walk.h) or k_walk_pairs (one warp per pair): the same choice as
-    // launch_staged_walk() makes -- the lane walk exists for the parameter sets that have seed records (PrmDefault's
-    // k-mer / extension constants, mqd <= SPEC_MAX_K); everything else is walked one warp per pair
-    if (lane_walk && PT::kSpecSeeds && P.mqd <= SPEC_MAX_K) return lane_walk_pair(pv, P, recs.data(), (uint32_t)list.size());
+    // k_walk_lanes (one lane per pair, lane_walk.h) or k_walk_pairs (one warp per pair).  The launcher uses the lane
+    // walk only for the parameter sets that have seed records (PrmDefault's constants, mqd <= SPEC_MAX_K); here every
+    // parameter set goes through it when asked to, so that its general code is checked beyond what the device runs
+    if (lane_walk) return lane_walk_pair(pv, P, recs.data(), (uint32_t)list.size());
     return walk_pair(w, pv, P, recs.data(), (uint32_t)list.size());
 }
 

@@ -121,6 +121,17 @@ def test_kernel_source_random_parameters_differential(emul, seed):
     assert np.array_equal(got, want), params
 
 
+@pytest.mark.parametrize("mal,msl", [(5, 7), (5, 4), (4, 7), (7, 7), (3, 3)])
+def test_short_anchors_matches_shorter_than_a_hit_run(emul, mal, msl):
+    """mal <= 7: a hit at (nearly) every position, runs of 8 hits per record, matches that end inside their own record's
+    run (the lane cursor must stay on that record), anchors shorter than a seed (mal < msl: found, never taken)."""
+    for seed in (300, 301, 302, 305):
+        names, seqs = synth.families(2, 3, 900, 2600, seed=seed, d_lo=0.02, d_hi=[0.06, 0.2, 0.4][seed % 3], block=(60, 300))
+        ss = hostio.SeqSet(names, seqs)
+        params = dict(mal=mal, msl=msl, mrd=40, mqd=40, reg=35, aw=15, am=7, ar=3)
+        assert np.array_equal(emul.run_rows(ss, params, threads=4), Oracle().run_rows(ss, params, threads=4)), (seed, params)
+
+
 @pytest.mark.parametrize("seed", list(range(230, 246)))
 def test_lane_walk_random_window_parameters_differential(emul, seed):
     """The default k-mer / extension constants (the parameter sets the lane walk and the seed records exist for) with
