@@ -133,6 +133,41 @@ def test_properties_at_bench_scale():
         m.close()
 
 
+@pytest.mark.parametrize("seed", list(range(60000, 60018)))
+def test_cuda_random_parameters_and_ragged_sets_differential(seed):
+    """The generators of the CPU fuzz (tests/test_emul.py) through the CUDA library: default parameters, random windows
+    with the default constants (lane walk, seed records or diagonal fallback), random everything (run-time parameter
+    kernels); ragged low-complexity sets every other seed.  All pairs against the oracle."""
+    from test_emul import _weird_sequence
+    rng = np.random.default_rng(seed)
+    if seed % 3 == 0:
+        params = None
+    elif seed % 3 == 1:
+        params = dict(mal=11, msl=7, mrd=int(rng.integers(1, 110)), mqd=int(rng.integers(0, 70)), reg=int(rng.integers(1, 80)),
+                      aw=15, am=7, ar=3)
+    else:
+        mal = int(rng.integers(3, 19))
+        params = dict(mal=mal, msl=int(rng.integers(2, min(mal + 3, 13))), mrd=int(rng.integers(1, 120)), mqd=int(rng.integers(0, 130)),
+                      reg=int(rng.integers(1, 90)), aw=int(rng.integers(1, 33)), am=int(rng.integers(0, 14)), ar=int(rng.integers(1, 7)))
+    if seed % 2:
+        base = rng.integers(0, 4, int(rng.integers(50, 3000)), dtype=np.uint8)
+        seqs = [base] + [_weird_sequence(rng, base) for _ in range(int(rng.integers(2, 5)))]
+        if seed % 7 == 0:
+            seqs.append(np.zeros(int(rng.integers(0, 12)), np.uint8))
+        names = [f"s{i}" for i in range(len(seqs))]
+    else:
+        names, seqs = synth.families(2, 4, 1500, 5000, seed=seed, d_lo=0.0 if seed % 4 == 0 else 0.02,
+                                     d_hi=[0.06, 0.2, 0.4][seed % 3], block=(60, 300))
+        seqs = [s.copy() for s in seqs]
+        a = int(rng.integers(0, 900))
+        seqs[2][a:a + int(rng.integers(1, 60))] = 4
+    ss = hostio.SeqSet(list(names), list(seqs))
+    got, _ = run_gpu(ss, params)
+    want = Oracle().run_rows(ss, params, threads=4)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert bad.size == 0, f"{params}: {bad.size}/{len(want)} pairs differ, first {bad[:5]}"
+
+
 def test_related_pairs_as_the_exception_and_as_the_rule(monkeypatch):
     """The lane walk hands related pairs to the warp-per-pair walk while they are at most a quarter of a chunk and keeps
     them otherwise (k_count_dense).  Both regimes, against the oracle on sampled rows and against the warp-per-pair
