@@ -73,3 +73,40 @@ def test_oracle_vs_reference_live(oracle, seed, params):
     a = RefShim().run_rows(ss, params)
     b = oracle.run_rows(ss, params)
     assert np.array_equal(a, b)
+
+
+@pytest.mark.skipif(not RefShim.available(), reason="oracle/_ref not built (no /root/reference here)")
+@pytest.mark.parametrize("seed", list(range(200000, 200048)))
+def test_oracle_vs_reference_random_parameters(oracle, seed):
+    """The oracle against the UNMODIFIED reference CParser on random parameter sets and ragged low-complexity sets (the
+    generators of tests/test_emul.py).  mqd is kept <= mrd: beyond that the reference reads seq_ref past its end
+    (compare_ranges_both_ways, parser.cpp:288, has no bound; a literal run of up to mqd positions behind the last
+    match may reach further than the mrd padding symbols at the end of seq_ref), so its own results depend on what the
+    heap holds there.  Offline: 4 325 sets with mqd <= mrd, no difference; 1 675 sets with mqd > mrd, 19 differ."""
+    from test_emul import _weird_sequence
+    rng = np.random.default_rng(seed)
+    if seed % 3 == 0:
+        params = None
+    elif seed % 3 == 1:
+        params = dict(mal=11, msl=7, mrd=int(rng.integers(1, 110)), mqd=int(rng.integers(0, 70)), reg=int(rng.integers(1, 80)),
+                      aw=15, am=7, ar=3)
+    else:
+        mal = int(rng.integers(3, 19))
+        params = dict(mal=mal, msl=int(rng.integers(2, min(mal + 3, 13))), mrd=int(rng.integers(1, 120)), mqd=int(rng.integers(0, 130)),
+                      reg=int(rng.integers(1, 90)), aw=int(rng.integers(1, 33)), am=int(rng.integers(0, 14)), ar=int(rng.integers(1, 7)))
+    if params is not None and params["mqd"] > params["mrd"]:
+        params["mqd"] = params["mrd"]
+    if seed % 2:
+        base = rng.integers(0, 4, int(rng.integers(50, 3000)), dtype=np.uint8)
+        seqs = [base] + [_weird_sequence(rng, base) for _ in range(int(rng.integers(2, 5)))]
+        if seed % 7 == 0:
+            seqs.append(np.zeros(int(rng.integers(0, 12)), np.uint8))
+        names = [f"s{i}" for i in range(len(seqs))]
+    else:
+        names, seqs = synth.families(2, 4, 1500, 5000, seed=seed, d_lo=0.0 if seed % 4 == 0 else 0.02,
+                                     d_hi=[0.06, 0.2, 0.4][seed % 3], block=(60, 300))
+        seqs = [s.copy() for s in seqs]
+        a = int(rng.integers(0, 900))
+        seqs[2][a:a + int(rng.integers(1, 60))] = 4
+    ss = hostio.SeqSet(list(names), list(seqs))
+    assert np.array_equal(oracle.run_rows(ss, params, threads=4), RefShim().run_rows(ss, params, threads=4)), params
