@@ -7,6 +7,8 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -64,7 +66,23 @@ void build_index(HostIndex& ix, const HostSeq& s, const Prm& P)
 // the staged pipeline of kernels.cu for one pair: k_scan_hits / k_expand_hits / k_hit_records element by
 // element, then the walk over the stored records (k_walk_pairs)
 template <class PT>
+std::vector<Rec> staged_records(const PairView& pv, const PT& P, uint32_t& n_recs);
+
+template <class PT>
 PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P, bool lane_walk)
+{
+    uint32_t n_recs = 0;
+    const std::vector<Rec> recs = staged_records(pv, P, n_recs);
+    // k_walk_lanes (one lane per pair, lane_walk.h) or k_walk_pairs (one warp per pair).  The launcher uses the lane
+    // walk only for the parameter sets that have seed records (PrmDefault's constants, mqd <= SPEC_MAX_K); here every
+    // parameter set goes through it when asked to, so that its general code is checked beyond what the device runs
+    if (lane_walk) return lane_walk_pair(pv, P, recs.data(), n_recs);
+    return walk_pair(w, pv, P, recs.data(), n_recs);
+}
+
+// the hit records of one pair as k_scan_* / k_expand_hits / k_hit_probe / k_hit_spec leave them
+template <class PT>
+std::vector<Rec> staged_records(const PairView& pv, const PT& P, uint32_t& n_recs)
 {
     const int n_loop = pv.Dq - P.msl;
     const int n_words = n_loop > 0 ? (n_loop + 31) / 32 : 0;
@@ -100,11 +118,8 @@ PairResult staged_pair(HostWarp& w, const PairView& pv, const PT& P, bool lane_w
     }
     for (size_t t = 0; t < list.size(); ++t)
         recs[t].x = (recs[t].x & (uint32_t)(LZ_STAGED_MAX_POS - 1)) | (link[t] << HIT_ENTRY_RUN_SHIFT);
-    // k_walk_lanes (one lane per pair, lane_walk.h) or k_walk_pairs (one warp per pair).  The launcher uses the lane
-    // walk only for the parameter sets that have seed records (PrmDefault's constants, mqd <= SPEC_MAX_K); here every
-    // parameter set goes through it when asked to, so that its general code is checked beyond what the device runs
-    if (lane_walk) return lane_walk_pair(pv, P, recs.data(), (uint32_t)list.size());
-    return walk_pair(w, pv, P, recs.data(), (uint32_t)list.size());
+    n_recs = (uint32_t)list.size();
+    return recs;
 }
 
 }  // namespace
@@ -315,6 +330,110 @@ extern "C" int lzani_emul_matrix_scan_check(const int32_t* p8, const uint8_t* re
         if (m != scan_word(pv, P, 32 * wd, n_loop)) ++bad;
     }
     return bad;
+}
+
+// ---- TEST ONLY: the segment-parallel walk of DESIGN.md section 8 ("few long pairs"), tried out on the host.
+// A walker started at an arbitrary record in the CLEAN state (no prediction, no open region) is claimed to merge
+// with the true walk at the first clean point both pass through, and to reproduce the true totals from there on.
+// Clean point: the walk is in anchor-search mode; its key is the query position of the next anchor event.  Totals
+// are taken with the pending region folded in (kept iff re - rs >= reg), as the next distant match would judge it.
+namespace {
+struct CleanPoint { int key; long m, x, n; int kept; };
+template <class PT>
+void walk_logged(LaneCtx L, const PT& P, std::vector<CleanPoint>& log, long fin[3])
+{
+    RecAhead none;
+    none.base = 0x80000000u;
+    for (int k = 0; k < 4; ++k) none.r[k] = Rec{0, 0, 0, 0};
+    int last_key = -2;
+    while (L.mode != LANE_DONE) {
+        if (L.s.pred < 0 && L.s.i < L.n_loop) {
+            LaneCtx C = L;
+            const int key = lane_next_event(C, C.s.i, LANE_NONE, false).qi;
+            if (key != last_key) {
+                const bool keep = L.s.rs >= 0 && L.s.re - L.s.rs >= P.reg;
+                log.push_back(CleanPoint{key, L.s.totM + (keep ? L.s.curM : 0), L.s.totX + (keep ? L.s.curX : 0), L.s.totN + (keep ? 1 : 0), keep ? L.s.re : L.s.kept_end});
+                last_key = key;
+            }
+        }
+        if (L.mode == LANE_RUN) lane_run_step(L, P, none);
+        else if (L.mode == LANE_SCAN) lane_scan_step(L, P);
+        else lane_slow_step(L, P);
+    }
+    fin[0] = L.s.totM; fin[1] = L.s.totX; fin[2] = L.s.totN;
+}
+}  // namespace
+
+// st[0] boundaries tried, st[1] walkers that merged with the true walk, st[2] of those: totals predicted wrongly,
+// st[3] sum over the merged walkers of (clean points of their own before the merge), st[4] merged walkers for which a fresh
+// walker started at the merge point WITH the true end of the last kept region reproduces the true totals (must be all)
+extern "C" int lzani_emul_segment_check(const int32_t* p8, const uint8_t* ref3, uint32_t ref_len, const uint8_t* qry3,
+                                        uint32_t qry_len, int n_segments, long* st)
+{
+    Prm P{p8[0], p8[1], p8[2], p8[3], p8[4], p8[5], p8[6], p8[7]};
+    HostSeq r, q;
+    build_seq(r, ref3, ref_len, P);
+    build_seq(q, qry3, qry_len, P);
+    HostIndex ix;
+    build_index(ix, r, P);
+    PairView pv;
+    pv.q = q.q.data(); pv.Dq = q.len + P.mrd;
+    pv.r = r.r.data(); pv.Dr = r_form_len(r.len, P.mrd);
+    pv.bitmap = ix.bitmap.data(); pv.bbits = ix.bbits;
+    pv.table = ix.table.data(); pv.tbits = ix.tbits;
+    uint32_t n = 0;
+    const std::vector<Rec> recs = staged_records(pv, P, n);
+    LaneCtx L0;
+    lane_begin(L0, pv, recs.data(), n, P.msl);
+    std::vector<CleanPoint> truth;
+    long fin[3];
+    walk_logged(L0, P, truth, fin);
+    for (int j = 1; j < n_segments && n; ++j) {
+        const uint32_t c = (uint32_t)((uint64_t)n * j / n_segments);
+        if (c == 0 || c >= n) continue;
+        ++st[0];
+        LaneCtx L;
+        lane_begin(L, pv, recs.data(), n, P.msl);
+        L.c = c;
+        L.s.i = rec_pos(recs[c]);
+        L.s.lit = P.mqd + 1;
+        std::vector<CleanPoint> mine;
+        long f2[3];
+        walk_logged(L, P, mine, f2);
+        // first clean point of this walker that the true walk also has
+        for (size_t a = 0; a < mine.size(); ++a) {
+            size_t b = 0;
+            while (b < truth.size() && truth[b].key != mine[a].key) ++b;
+            if (b == truth.size()) continue;
+            ++st[1];
+            st[3] += (long)a;
+            const long pm = truth[b].m + (f2[0] - mine[a].m), px = truth[b].x + (f2[1] - mine[a].x), pn = truth[b].n + (f2[2] - mine[a].n);
+            if (pm != fin[0] || px != fin[1] || pn != fin[2]) {
+                ++st[2];
+                if (getenv("LZ_SEGMENT_DEBUG"))
+                    fprintf(stderr, "segment %d/%d start rec %u key %d: predicted %ld %ld %ld, true %ld %ld %ld (true totals at the merge %ld %ld %ld, walker's %ld %ld %ld)\n",
+                            j, n_segments, c, mine[a].key, pm, px, pn, fin[0], fin[1], fin[2], truth[b].m, truth[b].x, truth[b].n, mine[a].m, mine[a].x, mine[a].n);
+            }
+            {
+                // a fresh walker in the clean state at the merge point, told the true end of the last kept region, must
+                // reproduce the rest of the true walk: the clean state + kept_end is ALL the state there is
+                LaneCtx L2;
+                lane_begin(L2, pv, recs.data(), n, P.msl);
+                uint32_t ck = 0;
+                while (ck < n && rec_pos(recs[ck]) + rec_run(recs[ck]) < mine[a].key) ++ck;
+                L2.c = ck;
+                L2.s.i = mine[a].key;
+                L2.s.lit = P.mqd + 1;
+                L2.s.kept_end = truth[b].kept;
+                std::vector<CleanPoint> again;
+                long f3[3];
+                walk_logged(L2, P, again, f3);
+                if (truth[b].m + f3[0] == fin[0] && truth[b].x + f3[1] == fin[1] && truth[b].n + f3[2] == fin[2]) ++st[4];
+            }
+            break;
+        }
+    }
+    return 0;
 }
 
 extern "C" int lzani_emul_q_recs(uint32_t len, int mrd) { return q_form_recs((int)len, mrd); }

@@ -285,3 +285,40 @@ def test_matrix_scan_equals_probe_scan(emul, params, request):
                 assert bad == 0, (r, q, bad)
                 checked += 1
     assert checked > (4 if big else 20)
+
+
+@pytest.mark.parametrize("kind", ["default", "long", "random"])
+def test_segment_parallel_walk_state_claim(emul, kind, request):
+    """NOT a product path: the claim behind the segment-parallel walk sketched in DESIGN.md section 8, checked with the
+    lane routines on the host (tests/emul: lzani_emul_segment_check).  A walker started at an arbitrary record in the
+    clean state (no prediction, no open region) meets the true walk at a clean point after about one clean point of
+    its own; from such a point on, a walker that knows the position AND the end of the last kept region reproduces the
+    true totals exactly (every merged boundary) -- so position + kept_end is all the state there is.  A walker that
+    assumes kept_end = 0 is wrong at 0-0.5 % of the boundaries (its first backward extension ran further back than
+    the true one may): that is what the stitch has to check.  150 sets per kind offline: 28 121 / 27 076 / 22 457 merged
+    boundaries, all reproduced."""
+    import ctypes as C
+    if "staged_lane" not in request.node.name:
+        pytest.skip("independent of the form of the parse under test: checked once")
+    f = emul.lib.lzani_emul_segment_check
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    st = (C.c_long * 5)()
+    for seed in range(700000, 700006):
+        rng = np.random.default_rng(seed)
+        params = {"default": None, "long": mg.LONGP,
+                  "random": dict(mal=int(rng.integers(6, 16)), msl=int(rng.integers(3, 10)), mrd=int(rng.integers(5, 100)),
+                                 mqd=int(rng.integers(0, 100)), reg=int(rng.integers(1, 90)), aw=int(rng.integers(1, 33)),
+                                 am=int(rng.integers(0, 14)), ar=int(rng.integers(1, 7)))}[kind]
+        names, seqs = synth.families(2, 3, 20000, 40000, seed=seed, d_lo=0.0 if seed % 4 == 0 else 0.02,
+                                     d_hi=[0.06, 0.2, 0.4][seed % 3], block=(200, 2000))
+        ss = hostio.SeqSet(names, seqs)
+        p8 = hostio.params_array(params)
+        for r in range(len(ss)):
+            for q in range(len(ss)):
+                if r != q:
+                    f(p8.ctypes.data, ss.packed[r].ctypes.data, int(ss.lens[r]), ss.packed[q].ctypes.data, int(ss.lens[q]), 8, st)
+    boundaries, merged, naive_wrong, exact_right = st[0], st[1], st[2], st[4]
+    assert boundaries >= 1000 and merged > 0.6 * boundaries
+    assert exact_right == merged
+    assert naive_wrong <= 0.02 * merged
+
